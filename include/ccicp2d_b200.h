@@ -1,0 +1,167 @@
+/* ccicp2d_b200.h -- C ABI of libccicp2d_b200.so: batched, B200-native (sm_100a)
+ * two-class point-to-point 2-D ICP.
+ *
+ * This is the drop-in boundary for ONE hot path of the servos/SLAM reference:
+ * the pair of calls at ccicp2d/src/icpTools.cpp:187-188
+ *     IcpPointToPoint icp(refGA, refNGA, nGA, nNGA, 2);
+ *     icp.fit(tarGA, tarNGA, nGA, nNGA, rot, trans, indist, 0);
+ * i.e. Icp::Icp (ccicp2d/src/icp.cpp:26-70), Icp::fit / fitIterate
+ * (icp.cpp:80-122), IcpPointToPoint::fitStep (icpPointToPoint.cpp:33-172),
+ * kdtree::KDTree::n_nearest(q,1) (kdtree.cpp:378-391, 515-683),
+ * IcpPointToPoint::getEdgeWeight (icpPointToPoint.cpp:233-316) and
+ * getNumberCorrespondences (:317-320).  The reference has no FFI of its own;
+ * its interface is the C++ class above.  include/ccicp2d/*.h re-declares that
+ * class on top of this ABI so ccicp2d/src/icpTools.cpp compiles unchanged
+ * (see INTEGRATION.md).
+ *
+ * Plain pointers and sizes only; no C++/torch types.  All functions return a
+ * CCICP_E_* code (0 = OK) and never abort or exit.  There is no CPU fallback:
+ * without a usable CUDA device every compute entry point fails with
+ * CCICP_E_NO_DEVICE / CCICP_E_CUDA.
+ */
+#ifndef CCICP2D_B200_H
+#define CCICP2D_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CCICP_ABI_VERSION 1
+
+/* ---- call-level error codes ------------------------------------------- */
+enum {
+  CCICP_OK = 0,
+  CCICP_E_INVALID = 1,     /* bad argument (NULL pointer, negative size, offsets not monotone) */
+  CCICP_E_NO_DEVICE = 2,   /* no CUDA device / device index out of range                        */
+  CCICP_E_CUDA = 3,        /* a CUDA runtime call failed; see ccicp_last_cuda_error              */
+  CCICP_E_NOMEM = 4,       /* host or device allocation failed                                   */
+  CCICP_E_TOO_LARGE = 5,   /* a scan exceeds the largest supported size (CCICP_MAX_POINTS)       */
+  CCICP_E_ARCH = 6         /* device is not sm_100 (the library carries sm_100a code only)       */
+};
+
+/* Largest number of points per class-pair cloud (model or scene, GA+NGA) the
+ * kernels accept.  The reference caps each class at 20000 points
+ * (ccicp2d/include/ccicp2d/icpTools.h:21). */
+#define CCICP_MAX_POINTS 65535
+
+/* ---- per-problem status bits (ccicp_result.status) -------------------- */
+enum {
+  CCICP_ST_TOO_FEW_MODEL = 1u << 0, /* nGA+nNGA < 5 model points: reference ctor bails (icp.cpp:37-43); R,t returned unchanged */
+  CCICP_ST_TOO_FEW_SCENE = 1u << 1, /* nGA+nNGA < 5 scene points: fit returns early (icp.cpp:100-103); R,t unchanged            */
+  CCICP_ST_NO_CORR       = 1u << 2, /* no iteration produced a correspondence (fitStep -1, icpPointToPoint.cpp:128-131)        */
+  CCICP_ST_REFLECTION    = 1u << 3, /* some iteration had det(H) < 0; like the reference (no det fix, icpPointToPoint.cpp:162)
+                                       the improper V*U^T was applied                                                         */
+  CCICP_ST_DEGENERATE    = 1u << 4, /* some iteration had a rank-deficient H (det == 0); result not comparable                 */
+  CCICP_ST_TIE_REPLAY    = 1u << 5, /* >= 1 query had several model points at the same float distance and was resolved by
+                                       replaying the reference kd-tree traversal (kdtree.cpp:515-683)                          */
+  CCICP_ST_CONVERGED     = 1u << 6, /* stopped because delta < min_delta (icp.cpp:119-120)                                     */
+  CCICP_ST_TREE_OVERFLOW = 1u << 7, /* tie replay needed a deeper kd-tree than the replay stack supports; tie left to the
+                                       grid's lowest-slot rule                                                                  */
+  CCICP_ST_INFO_SINGULAR = 1u << 8  /* getEdgeWeight's 3x3 system was singular / ss == 0; info[] holds inf/nan like the ref    */
+};
+
+/* ---- flags (ccicp_params.flags) ---------------------------------------- */
+enum {
+  CCICP_F_INFO           = 1u << 0, /* also compute the Lu-Milios information matrix (getEdgeWeight) into result.info         */
+  CCICP_F_INFO_FIXED_DY  = 1u << 1, /* use dy = ay - by instead of the reference's dy = ax - bx (icpPointToPoint.cpp:262)      */
+  CCICP_F_BEST_OF_SEEDS  = 1u << 2, /* n_seeds > 1: write one record per pair, the arg-min score seed (ties: lowest seed)       */
+  CCICP_F_NO_TIE_REPLAY  = 1u << 3, /* diagnostics only: skip the kd-tree tie replay (ties -> lowest grid slot)                 */
+  CCICP_F_EXACT_SUMS     = 1u << 4  /* reserved: sequential-order FP64 sums + restated NR SVD (bit-identical R,t)               */
+};
+
+typedef struct ccicp_params {
+  int32_t  max_iter;   /* Icp::setMaxIterations (icp.h:48); reference default 20 (icp.cpp:27)      */
+  uint32_t flags;      /* CCICP_F_*                                                                 */
+  double   min_delta;  /* Icp::setMinDeltaParam (icp.h:51); default 1e-6; < -1 => fixed iterations */
+  double   indist;     /* gate on the SQUARED float NN distance: keep iff (double)dis < indist
+                          (icpPointToPoint.cpp:76,111); the facade passes 5 (icpTools.cpp:188)      */
+  double   min_corr_frac; /* BEST_OF_SEEDS: a seed scores +inf unless num_corr >= frac * n_scene    */
+} ccicp_params;
+
+/* One record per (pair, seed) problem -- 160 bytes. */
+typedef struct ccicp_result {
+  double   R[4];        /* row-major 2x2: model = R * scene + t                                      */
+  double   t[2];
+  double   info[9];     /* row-major 3x3 getEdgeWeight output (valid iff CCICP_F_INFO)               */
+  double   last_delta;  /* return value of the last executed fitStep (-1 if it had no correspondences) */
+  double   score;       /* mean squared float NN distance over the correspondences of the last
+                           successful iteration (+inf if none)                                        */
+  int32_t  num_corr;    /* getNumberCorrespondences(): count of the last successful fitStep          */
+  int32_t  iters;       /* fitStep calls executed                                                    */
+  uint32_t status;      /* CCICP_ST_*                                                                */
+  int32_t  best_seed;   /* seed index this record belongs to                                         */
+  int32_t  n_tie_replays; /* queries resolved by the kd-tree replay, summed over iterations         */
+  int32_t  reserved;
+} ccicp_result;
+
+typedef struct ccicp_ctx ccicp_ctx;
+
+/* ---- lifetime ----------------------------------------------------------- */
+int  ccicp_abi_version(void);
+int  ccicp_create(ccicp_ctx** out, int device);
+int  ccicp_destroy(ccicp_ctx* ctx);
+const char* ccicp_strerror(int code);
+/* Text of the last CUDA error seen by this ctx (empty string if none). */
+const char* ccicp_last_cuda_error(const ccicp_ctx* ctx);
+void ccicp_default_params(ccicp_params* p);   /* max_iter 20, min_delta 1e-6, indist 5, flags 0 */
+
+/* ---- the hot path, host buffers ----------------------------------------
+ * Replaces, for every pair p (and every seed s of it), the two calls at
+ * ccicp2d/src/icpTools.cpp:187-188.
+ *
+ * Layout (CSR over pairs, points as interleaved x,y doubles exactly as the
+ * reference takes them, GA block first then NGA block):
+ *   model_off[2*n_pairs+1] : pair p's GA model points are [off[2p], off[2p+1]),
+ *                            its NGA model points [off[2p+1], off[2p+2])   (units: points)
+ *   model_xy [2*model_off[2*n_pairs]]
+ *   scene_off / scene_xy   : same for the scene ("template") clouds
+ *   init_Rt  [n_pairs*n_seeds][6] : {r00,r01,r10,r11,t0,t1} initial R,t (fit's in/out R,t)
+ *   out      [n_pairs*n_seeds]    (or [n_pairs] with CCICP_F_BEST_OF_SEEDS)
+ *   corr_idx : NULL, or [n_seeds][scene_off[2*n_pairs]] int32 (seed-major; with n_seeds == 1
+ *              simply one entry per scene point): per scene point the per-class model index
+ *              matched in the LAST executed iteration, -1 if gated / class skipped
+ *              (what KDTreeResult.idx holds, kdtree.h:31-35).
+ * Ownership: every buffer is caller-owned and only read/written during the
+ * call (the reference copies the model, icp.cpp:51-60, and borrows the scene).
+ * Synchronous.  Host memory may be pageable or pinned (ccicp_host_alloc).     */
+int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
+                         const double* model_xy, const int32_t* model_off,
+                         const double* scene_xy, const int32_t* scene_off,
+                         const double* init_Rt, const ccicp_params* params,
+                         ccicp_result* out, int32_t* corr_idx);
+
+/* ---- the hot path, device-resident buffers -------------------------------
+ * Same contract, but every pointer is a device pointer on ctx's device and the
+ * work is enqueued on `stream` (a cudaStream_t cast to void*; NULL = the
+ * ctx's own stream) without synchronising.  max_model / max_scene are the
+ * largest per-pair point counts (GA+NGA) in the batch, max_cells_hint may be
+ * 0.  Use ccicp_stream_sync (or your own event) before reading results.      */
+int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
+                                const double* d_model_xy, const int32_t* d_model_off,
+                                const double* d_scene_xy, const int32_t* d_scene_off,
+                                const double* d_init_Rt, const ccicp_params* params,
+                                ccicp_result* d_out, int32_t* d_corr_idx,
+                                int32_t max_model, int32_t max_scene, void* stream);
+int ccicp_stream_sync(ccicp_ctx* ctx, void* stream);
+
+/* Pinned host memory for callers that want the H2D/D2H copies to overlap. */
+int ccicp_host_alloc(void** out, size_t bytes);
+int ccicp_host_free(void* p);
+
+/* ---- introspection for benchmarks / tests -------------------------------- */
+typedef struct ccicp_launch_info {
+  int32_t grid, block, smem_bytes, regs_per_thread, blocks_per_sm, kernel_variant;
+  int32_t n_launches;          /* kernels launched by the last register call */
+  int32_t sm_count;
+  float   last_kernel_ms;      /* device time of the last register call's ICP kernel(s), CUDA events on its stream;
+                                  valid after a host-buffer call or after ccicp_stream_sync                      */
+  float   last_h2d_ms, last_d2h_ms;
+} ccicp_launch_info;
+int ccicp_get_launch_info(ccicp_ctx* ctx, ccicp_launch_info* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCICP2D_B200_H */

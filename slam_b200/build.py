@@ -1,0 +1,112 @@
+"""In-tree build of every native piece (no JIT cache: the .so files travel with
+the repo snapshot to the GPU box).
+
+  slam_b200/lib/libccicp2d_b200.so   product: sm_100a kernels + C ABI (nvcc)
+  slam_b200/lib/libccicp2d.so        product: header-compatible C++ facade (g++), links the above
+  slam_b200/lib/libscangen.so        workload generator (gcc)
+  tests/host/libkdreplay_host.so     host build of the tie-replay code, for CPU tests (g++)
+  oracle/libccicp_port.so            TEST INFRASTRUCTURE: C restatement (gcc)
+  oracle/_ref/libccicp_ref.so        TEST INFRASTRUCTURE: unmodified reference sources, only when
+                                     /root/reference is present (prebuilt file is used otherwise)
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "slam_b200", "csrc")
+LIB = os.path.join(ROOT, "slam_b200", "lib")
+MIN_BLOCKS = os.environ.get("CCICP_MIN_BLOCKS", "3")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-fmad=false",                       # parity: no FMA contraction anywhere (see ccicp_kernels.cuh)
+    "-DCCICP_MIN_BLOCKS=" + MIN_BLOCKS,
+    "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
+]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources if os.path.exists(s))
+
+
+def _run(cmd, verbose):
+    if verbose:
+        print("+", " ".join(cmd), flush=True)
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("build step failed: %s\n%s" % (" ".join(cmd), r.stdout))
+    if verbose and r.stdout.strip():
+        print(r.stdout)
+    return r.stdout
+
+
+def nvcc_path():
+    p = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(p):
+        raise RuntimeError("nvcc not found")
+    return p
+
+
+def build_cuda(force=False, verbose=False, extra=()):
+    os.makedirs(LIB, exist_ok=True)
+    out = os.path.join(LIB, "libccicp2d_b200.so")
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", "ccicp2d_b200.h"), __file__]
+    if force or _newer(out, srcs):
+        _run([nvcc_path()] + NVCC_FLAGS + list(extra) + ["-o", out, os.path.join(CSRC, "ccicp_api.cu")], verbose)
+    return out
+
+
+def build_facade(force=False, verbose=False):
+    out = os.path.join(LIB, "libccicp2d.so")
+    src = os.path.join(CSRC, "facade", "icp_facade.cpp")
+    if not os.path.exists(src):
+        return None
+    hdrs = [os.path.join(ROOT, "include", "ccicp2d", f) for f in os.listdir(os.path.join(ROOT, "include", "ccicp2d"))]
+    if force or _newer(out, [src] + hdrs):
+        _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"), "-o", out, src,
+              "-L" + LIB, "-lccicp2d_b200", "-Wl,-rpath,$ORIGIN"], verbose)
+    return out
+
+
+def build_scangen(force=False, verbose=False):
+    os.makedirs(LIB, exist_ok=True)
+    out = os.path.join(LIB, "libscangen.so")
+    srcs = [os.path.join(CSRC, "scangen.c"), os.path.join(CSRC, "scangen.h")]
+    if force or _newer(out, srcs):
+        _run(["gcc", "-O2", "-std=c11", "-fopenmp", "-fPIC", "-shared", "-o", out, srcs[0], "-lm"], verbose)
+    return out
+
+
+def build_host_tests(force=False, verbose=False):
+    d = os.path.join(ROOT, "tests", "host")
+    out = os.path.join(d, "libkdreplay_host.so")
+    srcs = [os.path.join(d, "kdreplay_host.cpp"), os.path.join(CSRC, "kdreplay.h")]
+    if force or _newer(out, srcs):
+        _run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", out, srcs[0]], verbose)
+    return out
+
+
+def build_oracle(force=False, verbose=False):
+    """Builds the checker (TEST INFRASTRUCTURE); building it is not using it."""
+    od = os.path.join(ROOT, "oracle")
+    if os.path.exists(os.path.join(od, "ccicp_port.c")):
+        _run(["make", "-C", od, "port"] + (["-B"] if force else []), verbose)
+    if os.path.isdir("/root/reference/ccicp2d/src"):
+        _run(["make", "-C", od, "ref"] + (["-B"] if force else []), verbose)
+
+
+def build_all(force=False, verbose=False):
+    build_cuda(force, verbose)
+    build_scangen(force, verbose)
+    build_facade(force, verbose)
+    build_host_tests(force, verbose)
+    build_oracle(force, verbose)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv, verbose=True)

@@ -1,0 +1,179 @@
+"""ctypes binding of include/ccicp2d_b200.h (libccicp2d_b200.so).
+
+The product path has no CPU fallback: if the library is missing, or there is no
+sm_100 device, these calls raise.  Host mirror of the reference's interface for
+the path lives in slam_b200/registration.py.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libccicp2d_b200.so")
+
+# error codes / status bits / flags (mirror the header)
+OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
+ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
+ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR = 32, 64, 128, 256
+F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS = 1, 2, 4, 8, 16
+
+
+class Params(C.Structure):
+    _fields_ = [("max_iter", C.c_int32), ("flags", C.c_uint32), ("min_delta", C.c_double),
+                ("indist", C.c_double), ("min_corr_frac", C.c_double)]
+
+
+class LaunchInfo(C.Structure):
+    _fields_ = [("grid", C.c_int32), ("block", C.c_int32), ("smem_bytes", C.c_int32),
+                ("regs_per_thread", C.c_int32), ("blocks_per_sm", C.c_int32), ("kernel_variant", C.c_int32),
+                ("n_launches", C.c_int32), ("sm_count", C.c_int32), ("last_kernel_ms", C.c_float),
+                ("last_h2d_ms", C.c_float), ("last_d2h_ms", C.c_float)]
+
+
+RESULT_DTYPE = np.dtype([("R", "<f8", (4,)), ("t", "<f8", (2,)), ("info", "<f8", (9,)), ("last_delta", "<f8"),
+                         ("score", "<f8"), ("num_corr", "<i4"), ("iters", "<i4"), ("status", "<u4"),
+                         ("best_seed", "<i4"), ("n_tie_replays", "<i4"), ("reserved", "<i4")])
+assert RESULT_DTYPE.itemsize == 160
+
+SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror", "ccicp_last_cuda_error",
+           "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
+           "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info"]
+
+_lib = None
+
+
+class CcicpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("ccicp error %d: %s" % (code, msg))
+        self.code = code
+
+
+def load():
+    """Loads the CUDA library; raises (never falls back) when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("%s is missing: run `python -m slam_b200.build` (there is no CPU fallback)" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, dbl = C.c_void_p, C.c_int32, C.c_double
+    lib.ccicp_abi_version.restype = C.c_int
+    lib.ccicp_create.argtypes = [C.POINTER(vp), C.c_int]
+    lib.ccicp_destroy.argtypes = [vp]
+    lib.ccicp_strerror.argtypes = [C.c_int]
+    lib.ccicp_strerror.restype = C.c_char_p
+    lib.ccicp_last_cuda_error.argtypes = [vp]
+    lib.ccicp_last_cuda_error.restype = C.c_char_p
+    lib.ccicp_default_params.argtypes = [C.POINTER(Params)]
+    lib.ccicp_default_params.restype = None
+    lib.ccicp_register_batch.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
+    lib.ccicp_register_batch_device.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, vp]
+    lib.ccicp_stream_sync.argtypes = [vp, vp]
+    lib.ccicp_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    lib.ccicp_host_free.argtypes = [vp]
+    lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
+    _lib = lib
+    return lib
+
+
+def default_params(**kw):
+    p = Params()
+    load().ccicp_default_params(C.byref(p))
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def fixed_iter_params(iters=30, flags=0, indist=5.0):
+    """BASELINE.json's setting: setMaxIterations(30) + setMinDeltaParam(-2)."""
+    return default_params(max_iter=iters, min_delta=-2.0, flags=flags, indist=indist)
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One ccicp_ctx: a device, a stream, grow-only device buffers."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.ccicp_create(C.byref(h), device)
+        if rc != OK:
+            raise CcicpError(rc, self.lib.ccicp_strerror(rc).decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ccicp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != OK:
+            msg = self.lib.ccicp_strerror(rc).decode()
+            extra = self.lib.ccicp_last_cuda_error(self.h).decode()
+            raise CcicpError(rc, msg + (" [" + extra + "]" if extra else ""))
+
+    def register_batch(self, model_xy, model_off, scene_xy, scene_off, init_Rt, params, n_seeds=1, want_corr=False,
+                       out=None, corr_out=None):
+        """Host-buffer call (ccicp_register_batch).  Arrays: float64 xy, int32 CSR offsets, float64 [n,6]."""
+        model_off = np.ascontiguousarray(model_off, np.int32)
+        scene_off = np.ascontiguousarray(scene_off, np.int32)
+        n_pairs = (len(model_off) - 1) // 2
+        model_xy = np.ascontiguousarray(model_xy, np.float64)
+        scene_xy = np.ascontiguousarray(scene_xy, np.float64)
+        init_Rt = np.ascontiguousarray(init_Rt, np.float64)
+        assert init_Rt.size == n_pairs * n_seeds * 6
+        best_of = bool(params.flags & F_BEST_OF_SEEDS) and n_seeds > 1
+        n_out = n_pairs if best_of else n_pairs * n_seeds
+        if out is None:
+            out = np.zeros(n_out, RESULT_DTYPE)
+        corr = None
+        if want_corr:
+            corr = corr_out if corr_out is not None else np.full((n_seeds, int(scene_off[-1])), -2, np.int32)
+        rc = self.lib.ccicp_register_batch(self.h, n_pairs, n_seeds, _ptr(model_xy), _ptr(model_off), _ptr(scene_xy),
+                                           _ptr(scene_off), _ptr(init_Rt), C.byref(params), _ptr(out), _ptr(corr))
+        self._check(rc)
+        return (out, corr) if want_corr else out
+
+    def register_batch_device(self, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt,
+                              params, d_out, d_corr, max_model, max_scene, stream=None):
+        """Device-pointer call (ints from tensor.data_ptr()); asynchronous on `stream` (cudaStream_t as int)."""
+        rc = self.lib.ccicp_register_batch_device(self.h, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy,
+                                                  d_scene_off, d_init_Rt, C.byref(params), d_out, d_corr or None,
+                                                  max_model, max_scene, stream or None)
+        self._check(rc)
+
+    def sync(self, stream=None):
+        self._check(self.lib.ccicp_stream_sync(self.h, stream or None))
+
+    def launch_info(self):
+        li = LaunchInfo()
+        self._check(self.lib.ccicp_get_launch_info(self.h, C.byref(li)))
+        return li
+
+
+def pinned_array(shape, dtype):
+    """numpy array backed by ccicp_host_alloc'd (page-locked) memory; keeps itself alive via .base."""
+    lib = load()
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    p = C.c_void_p()
+    rc = lib.ccicp_host_alloc(C.byref(p), max(n, 1))
+    if rc != OK:
+        raise CcicpError(rc, lib.ccicp_strerror(rc).decode())
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[id(buf)] = (buf, p)
+    return arr
+
+
+_PINNED = {}

@@ -1,0 +1,336 @@
+// ccicp_api.cu -- host side of libccicp2d_b200.so: the C ABI declared in
+// include/ccicp2d_b200.h.  CUDA runtime only (no torch, no CPU compute path).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "ccicp_pair_main.cuh"
+
+using namespace ccicp;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct ccicp_ctx {
+  int device = 0;
+  int sm_count = 0;
+  int max_smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
+  bool timed = false, timed_copies = false;
+  void* timed_stream = nullptr;
+  DevBuf counter, scratch, all_results;
+  DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
+  ccicp_launch_info info{};
+  std::string last_err;
+};
+
+namespace {
+
+int fail_cuda(ccicp_ctx* ctx, cudaError_t e, const char* what) {
+  if (ctx) ctx->last_err = std::string(what) + ": " + cudaGetErrorString(e);
+  cudaGetLastError();
+  return e == cudaErrorMemoryAllocation ? CCICP_E_NOMEM : CCICP_E_CUDA;
+}
+#define CK(call)                                              \
+  do {                                                        \
+    cudaError_t e_ = (call);                                  \
+    if (e_ != cudaSuccess) return fail_cuda(ctx, e_, #call);  \
+  } while (0)
+
+int reserve(ccicp_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return CCICP_OK;
+  if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) { b.p = nullptr; return fail_cuda(ctx, e, "cudaMalloc"); }
+  b.cap = want;
+  return CCICP_OK;
+}
+
+int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// worst-case number of grid cells for a pair with at most max_model model points
+int max_cells_for(int max_model) {
+  static const int lows[] = {0, 4, 33, 129, 513};
+  int best = 0;
+  for (int a : lows) {
+    if (a > max_model) break;
+    int b = max_model - a;
+    int ga = grid_side(a), gb = grid_side(b);
+    int c = ga * ga + gb * gb;
+    if (c > best) best = c;
+  }
+  return best;
+}
+
+int launch_icp(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy, const int32_t* d_model_off,
+               const double* d_scene_xy, const int32_t* d_scene_off, const double* d_init_Rt,
+               const ccicp_params* prm, ccicp_result* d_out, int32_t* d_corr, int32_t max_model, int32_t max_scene,
+               int32_t max_cells, int64_t total_scene, cudaStream_t st) {
+  ctx->info.n_launches = 0;
+  if (n_pairs == 0) return CCICP_OK;
+  if (max_model > CCICP_MAX_POINTS - 1 || max_scene > CCICP_MAX_POINTS) return CCICP_E_TOO_LARGE;
+  IcpArgs a{};
+  a.mcap = round_up(max_model < 32 ? 32 : max_model, 32);
+  a.scap = round_up(max_scene < 32 ? 32 : max_scene, 32);
+  a.ccap = max_cells > 0 ? max_cells : max_cells_for(max_model);
+  if (a.ccap < 64) a.ccap = 64;
+  const size_t smem = smem_bytes(a.mcap, a.scap, a.ccap);
+  if (smem > (size_t)ctx->max_smem_optin) return CCICP_E_TOO_LARGE;
+  CK(cudaFuncSetAttribute(icp_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_kernel, kThreads, smem));
+  if (occ < 1) return CCICP_E_TOO_LARGE;
+  const int resident = occ * ctx->sm_count;
+
+  const bool best_of = (prm->flags & CCICP_F_BEST_OF_SEEDS) && n_seeds > 1;
+  int items_per_pair = 1, seeds_per_item = n_seeds;
+  if (n_seeds > 1) {
+    long long want = (4LL * resident + n_pairs - 1) / n_pairs;
+    if (want < 1) want = 1;
+    if (want > n_seeds) want = n_seeds;
+    seeds_per_item = (int)((n_seeds + want - 1) / want);
+    items_per_pair = (n_seeds + seeds_per_item - 1) / seeds_per_item;
+  }
+  const long long n_items = (long long)n_pairs * items_per_pair;
+  const int grid = (int)(n_items < resident ? n_items : resident);
+
+  ccicp_result* kernel_out = d_out;
+  if (best_of) {
+    int rc = reserve(ctx, ctx->all_results, (size_t)n_pairs * n_seeds * sizeof(ccicp_result));
+    if (rc) return rc;
+    kernel_out = (ccicp_result*)ctx->all_results.p;
+  }
+  int rc = reserve(ctx, ctx->counter, 256);
+  if (rc) return rc;
+  const size_t per_cta = replay_scratch_bytes(max_model);
+  rc = reserve(ctx, ctx->scratch, per_cta * (size_t)grid);
+  if (rc) return rc;
+
+  a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
+  a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
+  a.work_counter = (int32_t*)ctx->counter.p;
+  a.scratch = (char*)ctx->scratch.p; a.scratch_per_cta = per_cta;
+  a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
+  a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
+  a.total_scene = total_scene; a.max_model = max_model;
+
+  CK(cudaMemsetAsync(ctx->counter.p, 0, 4, st));
+  CK(cudaEventRecord(ctx->ev[2], st));
+  icp_pair_kernel<<<grid, kThreads, smem, st>>>(a);
+  CK(cudaGetLastError());
+  ctx->info.n_launches = 1;
+  if (best_of) {
+    const int threads = 128, warps_per_block = threads / 32;
+    select_best_seed_kernel<<<(n_pairs + warps_per_block - 1) / warps_per_block, threads, 0, st>>>(
+        kernel_out, d_out, d_scene_off, n_pairs, n_seeds, prm->min_corr_frac);
+    CK(cudaGetLastError());
+    ctx->info.n_launches = 2;
+  }
+  CK(cudaEventRecord(ctx->ev[3], st));
+  ctx->timed = true; ctx->timed_stream = (void*)st;
+  cudaFuncAttributes fa;
+  CK(cudaFuncGetAttributes(&fa, icp_pair_kernel));
+  ctx->info.grid = grid; ctx->info.block = kThreads; ctx->info.smem_bytes = (int)smem;
+  ctx->info.regs_per_thread = fa.numRegs; ctx->info.blocks_per_sm = occ; ctx->info.kernel_variant = 0;
+  ctx->info.sm_count = ctx->sm_count;
+  return CCICP_OK;
+}
+
+bool offsets_ok(const int32_t* off, int32_t n_pairs) {
+  if (off[0] < 0) return false;
+  for (int64_t i = 0; i < 2 * (int64_t)n_pairs; i++)
+    if (off[i + 1] < off[i]) return false;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ccicp_abi_version(void) { return CCICP_ABI_VERSION; }
+
+const char* ccicp_strerror(int code) {
+  switch (code) {
+    case CCICP_OK: return "ok";
+    case CCICP_E_INVALID: return "invalid argument";
+    case CCICP_E_NO_DEVICE: return "no usable CUDA device (this library has no CPU path)";
+    case CCICP_E_CUDA: return "CUDA runtime error";
+    case CCICP_E_NOMEM: return "out of memory";
+    case CCICP_E_TOO_LARGE: return "scan too large for the on-chip pair kernel";
+    case CCICP_E_ARCH: return "device is not compute capability 10.x (library is built for sm_100a only)";
+    default: return "unknown error";
+  }
+}
+
+const char* ccicp_last_cuda_error(const ccicp_ctx* ctx) { return ctx ? ctx->last_err.c_str() : ""; }
+
+void ccicp_default_params(ccicp_params* p) {
+  if (!p) return;
+  p->max_iter = 20;          // icp.cpp:27
+  p->flags = 0;
+  p->min_delta = 1e-6;       // icp.cpp:27
+  p->indist = 5.0;           // icpTools.cpp:188
+  p->min_corr_frac = 0.5;
+}
+
+int ccicp_create(ccicp_ctx** out, int device) {
+  if (!out) return CCICP_E_INVALID;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) { cudaGetLastError(); return CCICP_E_NO_DEVICE; }
+  if (device < 0 || device >= n) return CCICP_E_NO_DEVICE;
+  ccicp_ctx* ctx = new (std::nothrow) ccicp_ctx();
+  if (!ctx) return CCICP_E_NOMEM;
+  ctx->device = device;
+  cudaDeviceProp prop;
+  if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+    delete ctx; cudaGetLastError(); return CCICP_E_CUDA;
+  }
+  if (prop.major != 10) { delete ctx; return CCICP_E_ARCH; }
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
+  for (auto& ev : ctx->ev)
+    if (cudaEventCreate(&ev) != cudaSuccess) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
+  *out = ctx;
+  return CCICP_OK;
+}
+
+int ccicp_destroy(ccicp_ctx* ctx) {
+  if (!ctx) return CCICP_OK;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
+                    &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr};
+  for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
+  for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return CCICP_OK;
+}
+
+int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy,
+                                const int32_t* d_model_off, const double* d_scene_xy, const int32_t* d_scene_off,
+                                const double* d_init_Rt, const ccicp_params* params, ccicp_result* d_out,
+                                int32_t* d_corr_idx, int32_t max_model, int32_t max_scene, void* stream) {
+  if (!ctx || !params || n_pairs < 0 || n_seeds < 1 || max_model < 0 || max_scene < 0) return CCICP_E_INVALID;
+  if (n_pairs > 0 && (!d_model_xy || !d_model_off || !d_scene_xy || !d_scene_off || !d_init_Rt || !d_out)) return CCICP_E_INVALID;
+  if (d_corr_idx && n_seeds > 1 && (params->flags & CCICP_F_BEST_OF_SEEDS)) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  int64_t total_scene = 0;
+  if (d_corr_idx && n_seeds > 1 && n_pairs > 0) {   // seed stride of corr_idx: needs the batch total
+    int32_t last = 0;
+    CK(cudaMemcpyAsync(&last, d_scene_off + 2 * (size_t)n_pairs, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    total_scene = last;
+  }
+  ctx->timed_copies = false;
+  return launch_icp(ctx, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt, params, d_out,
+                    d_corr_idx, max_model, max_scene, 0, total_scene, st);
+}
+
+int ccicp_stream_sync(ccicp_ctx* ctx, void* stream) {
+  if (!ctx) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(stream ? (cudaStream_t)stream : ctx->stream));
+  return CCICP_OK;
+}
+
+int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* model_xy,
+                         const int32_t* model_off, const double* scene_xy, const int32_t* scene_off,
+                         const double* init_Rt, const ccicp_params* params, ccicp_result* out, int32_t* corr_idx) {
+  if (!ctx || !params || n_pairs < 0 || n_seeds < 1) return CCICP_E_INVALID;
+  if (n_pairs == 0) return CCICP_OK;
+  if (!model_off || !scene_off || !init_Rt || !out) return CCICP_E_INVALID;
+  if (!offsets_ok(model_off, n_pairs) || !offsets_ok(scene_off, n_pairs)) return CCICP_E_INVALID;
+  const bool best_of = (params->flags & CCICP_F_BEST_OF_SEEDS) && n_seeds > 1;
+  if (corr_idx && best_of) return CCICP_E_INVALID;
+  const int64_t m_base = model_off[0], s_base = scene_off[0];
+  const int64_t n_model = model_off[2 * (size_t)n_pairs] - m_base, n_scene = scene_off[2 * (size_t)n_pairs] - s_base;
+  if ((n_model > 0 && !model_xy) || (n_scene > 0 && !scene_xy)) return CCICP_E_INVALID;
+  if (m_base != 0 || s_base != 0) return CCICP_E_INVALID;   // offsets are absolute into the arrays passed
+  int max_model = 0, max_scene = 0, max_cells = 0;
+  for (int32_t p = 0; p < n_pairs; p++) {
+    const int a = model_off[2 * p + 1] - model_off[2 * p], b = model_off[2 * p + 2] - model_off[2 * p + 1];
+    const int c = scene_off[2 * p + 2] - scene_off[2 * p];
+    if (a + b > max_model) max_model = a + b;
+    if (c > max_scene) max_scene = c;
+    const int ga = grid_side(a), gb = grid_side(b);
+    if (ga * ga + gb * gb > max_cells) max_cells = ga * ga + gb * gb;
+  }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const size_t n_prob = (size_t)n_pairs * n_seeds, n_out = best_of ? (size_t)n_pairs : n_prob;
+  const size_t off_bytes = (2 * (size_t)n_pairs + 1) * 4;
+  int rc;
+  if ((rc = reserve(ctx, ctx->d_model, (size_t)n_model * 16 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->d_scene, (size_t)n_scene * 16 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->d_moff, off_bytes))) return rc;
+  if ((rc = reserve(ctx, ctx->d_soff, off_bytes))) return rc;
+  if ((rc = reserve(ctx, ctx->d_init, n_prob * 48))) return rc;
+  if ((rc = reserve(ctx, ctx->d_out, n_out * sizeof(ccicp_result)))) return rc;
+  if (corr_idx && (rc = reserve(ctx, ctx->d_corr, (size_t)n_scene * n_seeds * 4 + 16))) return rc;
+
+  CK(cudaEventRecord(ctx->ev[0], st));
+  if (n_model) CK(cudaMemcpyAsync(ctx->d_model.p, model_xy, (size_t)n_model * 16, cudaMemcpyHostToDevice, st));
+  if (n_scene) CK(cudaMemcpyAsync(ctx->d_scene.p, scene_xy, (size_t)n_scene * 16, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_moff.p, model_off, off_bytes, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_soff.p, scene_off, off_bytes, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_init.p, init_Rt, n_prob * 48, cudaMemcpyHostToDevice, st));
+  CK(cudaEventRecord(ctx->ev[1], st));
+  rc = launch_icp(ctx, n_pairs, n_seeds, (const double*)ctx->d_model.p, (const int32_t*)ctx->d_moff.p,
+                  (const double*)ctx->d_scene.p, (const int32_t*)ctx->d_soff.p, (const double*)ctx->d_init.p, params,
+                  (ccicp_result*)ctx->d_out.p, corr_idx ? (int32_t*)ctx->d_corr.p : nullptr, max_model, max_scene,
+                  max_cells, n_scene, st);
+  if (rc) return rc;
+  CK(cudaEventRecord(ctx->ev[4], st));
+  CK(cudaMemcpyAsync(out, ctx->d_out.p, n_out * sizeof(ccicp_result), cudaMemcpyDeviceToHost, st));
+  if (corr_idx && n_scene) CK(cudaMemcpyAsync(corr_idx, ctx->d_corr.p, (size_t)n_scene * n_seeds * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(ctx->ev[5], st));
+  CK(cudaStreamSynchronize(st));
+  ctx->timed_copies = true;
+  return CCICP_OK;
+}
+
+int ccicp_host_alloc(void** out, size_t bytes) {
+  if (!out) return CCICP_E_INVALID;
+  *out = nullptr;
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+  if (e != cudaSuccess) { cudaGetLastError(); *out = nullptr; return e == cudaErrorMemoryAllocation ? CCICP_E_NOMEM : CCICP_E_CUDA; }
+  return CCICP_OK;
+}
+
+int ccicp_host_free(void* p) {
+  if (!p) return CCICP_OK;
+  cudaError_t e = cudaFreeHost(p);
+  if (e != cudaSuccess) { cudaGetLastError(); return CCICP_E_CUDA; }
+  return CCICP_OK;
+}
+
+int ccicp_get_launch_info(ccicp_ctx* ctx, ccicp_launch_info* out) {
+  if (!ctx || !out) return CCICP_E_INVALID;
+  if (ctx->timed) {
+    if (cudaEventQuery(ctx->ev[3]) == cudaSuccess) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]) == cudaSuccess) ctx->info.last_kernel_ms = ms;
+      if (ctx->timed_copies && cudaEventQuery(ctx->ev[5]) == cudaSuccess) {
+        if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) ctx->info.last_h2d_ms = ms;
+        if (cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]) == cudaSuccess) ctx->info.last_d2h_ms = ms;
+      }
+    }
+    cudaGetLastError();
+  }
+  *out = ctx->info;
+  return CCICP_OK;
+}
+
+}  // extern "C"

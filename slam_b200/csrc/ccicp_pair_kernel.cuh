@@ -1,0 +1,195 @@
+// ccicp_pair_kernel.cuh -- the persistent one-CTA-per-pair ICP kernel.
+#pragma once
+#include "ccicp_kernels.cuh"
+
+namespace ccicp {
+
+// ---- grid build: counting (single-digit radix) sort of the model on cell id -
+// a1 (icp.cpp:51-60): model doubles are rounded to float once, here.
+__device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int m0, int nGA, int nNGA, int tid) {
+  const int nm = nGA + nNGA;
+  const int G0 = grid_side(nGA), G1 = grid_side(nNGA);
+  const int ncell = G0 * G0 + G1 * G1;
+  float2* tmp_pts = (float2*)s.scene;
+  uint16_t* tmp_cell = (uint16_t*)(tmp_pts + a.mcap);
+  uint16_t* tmp_rank = tmp_cell + a.mcap;
+  uint32_t* cnt32 = (uint32_t*)s.cstart;
+  for (int j = tid; j < (ncell + 4) / 2; j += kThreads) cnt32[j] = 0u;
+  if (tid < 8) s.misc[M_BBOX + tid] = (tid & 2) ? INT_MIN : INT_MAX;
+  if (tid < 2) { s.misc[M_TREE + tid] = 0; s.misc[M_NNODE + tid] = 0; }
+  __syncthreads();
+
+  // load + round + per-class bounding box
+  int bb[8] = {INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MAX, INT_MAX, INT_MIN, INT_MIN};
+  const double2* src = (const double2*)a.model_xy + m0;
+  for (int i = tid; i < nm; i += kThreads) {
+    double2 p = __ldg(src + i);
+    float2 f = make_float2(__double2float_rn(p.x), __double2float_rn(p.y));
+    tmp_pts[i] = f;
+    const int c4 = (i >= nGA) ? 4 : 0;
+    const int ox = f2ord(f.x), oy = f2ord(f.y);
+    bb[c4 + 0] = min(bb[c4 + 0], ox); bb[c4 + 1] = min(bb[c4 + 1], oy);
+    bb[c4 + 2] = max(bb[c4 + 2], ox); bb[c4 + 3] = max(bb[c4 + 3], oy);
+  }
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    int v = (k & 2) ? __reduce_max_sync(0xffffffffu, bb[k]) : __reduce_min_sync(0xffffffffu, bb[k]);
+    if ((tid & 31) == 0) {
+      if (k & 2) atomicMax(&s.misc[M_BBOX + k], v); else atomicMin(&s.misc[M_BBOX + k], v);
+    }
+  }
+  __syncthreads();
+
+  if (tid < 2) {
+    GridP g;
+    const int n = tid ? nNGA : nGA;
+    g.G = tid ? G1 : G0;
+    g.base = tid ? G0 * G0 : 0;
+    g.n = n;
+    g.first = tid ? nGA : 0;
+    g.minx = g.miny = 0.0f; g.h = 1.0f; g.inv_h = 1.0f;
+    if (g.G > 0) {
+      const float minx = ord2f(s.misc[M_BBOX + 4 * tid + 0]), miny = ord2f(s.misc[M_BBOX + 4 * tid + 1]);
+      const float maxx = ord2f(s.misc[M_BBOX + 4 * tid + 2]), maxy = ord2f(s.misc[M_BBOX + 4 * tid + 3]);
+      float ext = fmaxf(maxx - minx, maxy - miny);
+      if (!(ext > 1.0e-6f)) ext = 1.0e-6f;
+      g.minx = minx; g.miny = miny;
+      g.h = ext / (float)g.G;
+      g.inv_h = (float)g.G / ext;
+    }
+    s.grid[tid] = g;
+  }
+  __syncthreads();
+
+  // histogram: two 16-bit counters per 32-bit word; the returned old value is the rank in the cell
+  for (int i = tid; i < nm; i += kThreads) {
+    const GridP& g = s.grid[i >= nGA];
+    if (g.G == 0) continue;
+    float2 f = tmp_pts[i];
+    int ix = (int)__fmul_rn(__fsub_rn(f.x, g.minx), g.inv_h);
+    int iy = (int)__fmul_rn(__fsub_rn(f.y, g.miny), g.inv_h);
+    ix = min(max(ix, 0), g.G - 1); iy = min(max(iy, 0), g.G - 1);
+    const int cell = g.base + iy * g.G + ix;
+    const int sh = (cell & 1) * 16;
+    uint32_t old = atomicAdd(&cnt32[cell >> 1], 1u << sh);
+    tmp_cell[i] = (uint16_t)cell;
+    tmp_rank[i] = (uint16_t)((old >> sh) & 0xffffu);
+  }
+  __syncthreads();
+
+  // exclusive scan of the ncell+1 counters, in place
+  {
+    const int n_ent = ncell + 1;
+    const int ch = (n_ent + kThreads - 1) / kThreads;
+    const int beg = min(tid * ch, n_ent), end = min(beg + ch, n_ent);
+    uint32_t sum = 0;
+    for (int j = beg; j < end; j++) sum += s.cstart[j];
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((tid & 31) >= o) incl += v;
+    }
+    uint32_t* wtot = (uint32_t*)s.red;
+    if ((tid & 31) == 31) wtot[tid >> 5] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int w = 0; w < (tid >> 5); w++) woff += wtot[w];
+    uint32_t run = woff + incl - sum;
+    for (int j = beg; j < end; j++) { uint32_t c = s.cstart[j]; s.cstart[j] = (uint16_t)run; run += c; }
+  }
+  __syncthreads();
+
+  for (int i = tid; i < nm; i += kThreads) {
+    const int cls = i >= nGA;
+    if (s.grid[cls].G == 0) continue;
+    const int slot = s.cstart[tmp_cell[i]] + tmp_rank[i];
+    s.mpts[slot] = tmp_pts[i];
+    s.morig[slot] = (uint16_t)(i - (cls ? nGA : 0));
+  }
+  __syncthreads();
+}
+
+// ---- tie replay (rare): rebuild the reference kd-tree, re-answer tied queries
+struct ReplayScratch { kdreplay::Pt* pts; int32_t* ind; kdreplay::Node* nodes; };
+
+__device__ __forceinline__ ReplayScratch replay_scratch(const IcpArgs& a) {
+  char* base = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta;
+  ReplayScratch r;
+  r.nodes = (kdreplay::Node*)base;
+  base += align_up((size_t)(2 * a.max_model + 8) * sizeof(kdreplay::Node), 16);
+  r.pts = (kdreplay::Pt*)base;
+  base += align_up((size_t)a.max_model * sizeof(kdreplay::Pt), 16);
+  r.ind = (int32_t*)base;
+  return r;
+}
+__host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
+  return align_up((size_t)(2 * max_model + 8) * sizeof(kdreplay::Node), 16) +
+         align_up((size_t)max_model * sizeof(kdreplay::Pt), 16) + align_up((size_t)max_model * 4, 16);
+}
+
+__device__ __noinline__ void replay_ties(const IcpArgs& a, const Smem& s, const double* Rt, int m0, int nGA, int nNGA,
+                                         int ns, int nsGA, uint32_t pend, int tid) {
+  const int nm = nGA + nNGA;
+  ReplayScratch rs = replay_scratch(a);
+  const bool need_build = (s.grid[0].G > 0 && s.misc[M_TREE + 0] == 0) || (s.grid[1].G > 0 && s.misc[M_TREE + 1] == 0);
+  __syncthreads();
+  if (need_build) {
+    const double2* src = (const double2*)a.model_xy + m0;
+    for (int i = tid; i < nm; i += kThreads) {
+      double2 p = src[i];
+      rs.pts[i].x = __double2float_rn(p.x); rs.pts[i].y = __double2float_rn(p.y);
+    }
+    __syncthreads();
+    if (tid < 2 && s.grid[tid].G > 0 && s.misc[M_TREE + tid] == 0) {      // one thread per class
+      const int first = s.grid[tid].first, n = s.grid[tid].n;
+      int nn = 0;
+      int rc = kdreplay::build(rs.pts + first, n, rs.ind + first, rs.nodes + 2 * first + 4 * tid, 2 * n + 4, &nn);
+      s.misc[M_NNODE + tid] = nn;
+      s.misc[M_TREE + tid] = (rc == kdreplay::OK) ? 1 : 2;
+      if (rc != kdreplay::OK) atomicOr(&s.misc[M_TREEFAIL], 1);
+    }
+    __syncthreads();
+  }
+  int k = 0;
+  for (int i = tid; i < ns; i += kThreads, k++) {
+    if (!((pend >> k) & 1u)) continue;
+    const int cls = i >= nsGA;
+    const GridP& g = s.grid[cls];
+    if (s.misc[M_TREE + cls] != 1) continue;              // tree unavailable: keep the grid's answer
+    double2 sp = s.scene[i];
+    float qx, qy;
+    transform(Rt, sp.x, sp.y, qx, qy);
+    int32_t o = -1; float d = 0.0f;
+    int rc = kdreplay::nearest(rs.pts + g.first, rs.ind + g.first, rs.nodes + 2 * g.first + 4 * cls,
+                               s.misc[M_NNODE + cls], qx, qy, &o, &d);
+    if (rc != kdreplay::OK || o < 0) { atomicOr(&s.misc[M_TREEFAIL], 1); continue; }
+    // original index -> sorted slot: look inside the point's own cell
+    kdreplay::Pt p = rs.pts[g.first + o];
+    int ix = (int)__fmul_rn(__fsub_rn(p.x, g.minx), g.inv_h);
+    int iy = (int)__fmul_rn(__fsub_rn(p.y, g.miny), g.inv_h);
+    ix = min(max(ix, 0), g.G - 1); iy = min(max(iy, 0), g.G - 1);
+    const int cell = g.base + iy * g.G + ix;
+    for (int j = s.cstart[cell]; j < s.cstart[cell + 1]; j++)
+      if (s.morig[j] == (uint16_t)o) { s.slots[i] = (uint16_t)j; break; }
+    atomicAdd(&s.misc[M_REPLAYS], 1);
+  }
+  __syncthreads();
+}
+
+// pass-1 partial sums recomputed from slots[] (used after a tie replay)
+__device__ __forceinline__ void pass1_from_slots(const Smem& s, const double* Rt, int ns, int tid,
+                                                 double& smx, double& smy, double& stx, double& sty, int& cnt) {
+  smx = smy = stx = sty = 0.0; cnt = 0;
+  for (int i = tid; i < ns; i += kThreads) {
+    const unsigned slot = s.slots[i];
+    if (slot == kNoSlot) continue;
+    double2 sp = s.scene[i];
+    float qx, qy;
+    transform(Rt, sp.x, sp.y, qx, qy);
+    float2 m = s.mpts[slot];
+    smx += (double)m.x; smy += (double)m.y; stx += (double)qx; sty += (double)qy; cnt++;
+  }
+}
+
+}  // namespace ccicp

@@ -1,0 +1,326 @@
+// ccicp_pair_main.cuh -- kernel entry: persistent CTAs pull (pair, seed-chunk)
+// work items from an atomic counter; each item = grid build once + all
+// iterations of every seed in the chunk, entirely in shared memory/registers.
+#pragma once
+#include "ccicp_pair_kernel.cuh"
+
+namespace ccicp {
+
+// block-wide sum of up to NV doubles per thread (+ two ints); result broadcast
+// to every thread in a fixed order (deterministic run to run).
+template <int NV>
+__device__ __forceinline__ void block_reduce(double* red, int off, double (&v)[NV], int tid) {
+#pragma unroll
+  for (int k = 0; k < NV; k++) v[k] = warp_sum(v[k]);
+  if ((tid & 31) == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) red[(tid >> 5) * 10 + off + k] = v[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) t += red[w * 10 + off + k];
+    v[k] = t;
+  }
+}
+
+// a8 + a9.  Closed form of R_ = V*U^T for the 2x2 H = sum q_t^T q_m
+// (icpPointToPoint.cpp:159-163): a rotation when det H > 0, the improper
+// (reflection) polar factor when det H < 0 -- the reference applies no det fix.
+__device__ __forceinline__ double solve_and_compose(const double* H, const double* mu_m, const double* mu_t,
+                                                    double* Rt, uint32_t& status) {
+  const double det = H[0] * H[3] - H[1] * H[2];
+  double r00, r01, r10, r11;
+  if (det >= 0.0) {
+    const double A = H[0] + H[3], B = H[1] - H[2];
+    const double r = sqrt(A * A + B * B);
+    if (det == 0.0 || !(r > 0.0)) status |= CCICP_ST_DEGENERATE;
+    const double c = r > 0.0 ? A / r : 1.0, s = r > 0.0 ? B / r : 0.0;
+    r00 = c; r01 = -s; r10 = s; r11 = c;
+  } else {
+    status |= CCICP_ST_REFLECTION;
+    const double A = H[0] - H[3], B = H[1] + H[2];
+    const double r = sqrt(A * A + B * B);
+    const double c = r > 0.0 ? A / r : 1.0, s = r > 0.0 ? B / r : 0.0;
+    r00 = c; r01 = s; r10 = s; r11 = -c;
+  }
+  const double t0 = mu_m[0] - (r00 * mu_t[0] + r01 * mu_t[1]);
+  const double t1 = mu_m[1] - (r10 * mu_t[0] + r11 * mu_t[1]);
+  // compose: R = R_*R ; t = R_*t + t_   (icpPointToPoint.cpp:166-167)
+  const double n00 = r00 * Rt[0] + r01 * Rt[2], n01 = r00 * Rt[1] + r01 * Rt[3];
+  const double n10 = r10 * Rt[0] + r11 * Rt[2], n11 = r10 * Rt[1] + r11 * Rt[3];
+  const double nt0 = (r00 * Rt[4] + r01 * Rt[5]) + t0, nt1 = (r10 * Rt[4] + r11 * Rt[5]) + t1;
+  Rt[0] = n00; Rt[1] = n01; Rt[2] = n10; Rt[3] = n11; Rt[4] = nt0; Rt[5] = nt1;
+  // delta = max(||R_-I||_F, ||t_||_2)   (icpPointToPoint.cpp:170, matrix.cpp:354-360)
+  const double a = r00 - 1.0, d = r11 - 1.0;
+  const double nr = sqrt(a * a + r01 * r01 + r10 * r10 + d * d);
+  const double nt = sqrt(t0 * t0 + t1 * t1);
+  return nr > nt ? nr : nt;
+}
+
+__global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(const IcpArgs a) {
+  extern __shared__ __align__(16) char smem_raw[];
+  const Smem s = carve(smem_raw, a.mcap, a.scap, a.ccap);
+  const int tid = threadIdx.x;
+  const float gate_f = __double2float_ru(a.indist);
+  const bool replay_on = !(a.flags & CCICP_F_NO_TIE_REPLAY);
+  const int n_items = a.n_pairs * a.items_per_pair;
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) s.misc[M_WORK] = atomicAdd(a.work_counter, 1);
+    __syncthreads();
+    const int item = s.misc[M_WORK];
+    if (item >= n_items) break;
+    const int pair = item / a.items_per_pair;
+    const int seed0 = (item - pair * a.items_per_pair) * a.seeds_per_item;
+    const int seed1 = min(seed0 + a.seeds_per_item, a.n_seeds);
+
+    const int m0 = a.model_off[2 * pair], nmGA = a.model_off[2 * pair + 1] - m0, nmNGA = a.model_off[2 * pair + 2] - a.model_off[2 * pair + 1];
+    const int s0 = a.scene_off[2 * pair], nsGA = a.scene_off[2 * pair + 1] - s0, nsNGA = a.scene_off[2 * pair + 2] - a.scene_off[2 * pair + 1];
+    const int ns = nsGA + nsNGA;
+    const bool model_ok = nmGA + nmNGA >= 5, scene_ok = ns >= 5;
+
+    if (model_ok && scene_ok) {
+      build_grid(a, s, m0, nmGA, nmNGA, tid);
+      const double2* src = (const double2*)a.scene_xy + s0;
+      for (int i = tid; i < ns; i += kThreads) s.scene[i] = __ldg(src + i);
+      // each thread only ever reads back the scene points it loaded itself
+    }
+
+    for (int seed = seed0; seed < seed1; seed++) {
+      const size_t prob = (size_t)pair * a.n_seeds + seed;
+      double Rt[6];
+#pragma unroll
+      for (int k = 0; k < 6; k++) Rt[k] = __ldg(a.init_Rt + prob * 6 + k);
+      uint32_t status = 0;
+      int iters = 0, num_corr = 0;
+      double last_delta = 0.0;
+      bool have_ok = false, last_failed = false;
+      __syncthreads();
+      if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; }
+
+      if (!model_ok) status |= CCICP_ST_TOO_FEW_MODEL;
+      else if (!scene_ok) status |= CCICP_ST_TOO_FEW_SCENE;
+      else {
+        for (int iter = 0; iter < a.max_iter; iter++) {
+          // ---- a4..a6: transform, nearest neighbour, gate; pass-1 partial sums
+          double v1[4] = {0.0, 0.0, 0.0, 0.0};
+          int cnt = 0;
+          uint32_t pend = 0;
+          int k = 0;
+          for (int i = tid; i < ns; i += kThreads, k++) {
+            const double2 sp = s.scene[i];
+            float qx, qy;
+            transform(Rt, sp.x, sp.y, qx, qy);
+            const GridP& g = s.grid[i >= nsGA];
+            unsigned slot = kNoSlot;
+            if (g.G > 0) {
+              float best; int bslot, tie;
+              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, best, bslot, tie);
+              if (bslot >= 0 && (double)best < a.indist) {
+                slot = (unsigned)bslot;
+                if (tie && replay_on) pend |= 1u << (k & 31);
+              }
+            }
+            s.slots[i] = (uint16_t)slot;
+            if (slot != kNoSlot) {
+              const float2 m = s.mpts[slot];
+              v1[0] += (double)m.x; v1[1] += (double)m.y; v1[2] += (double)qx; v1[3] += (double)qy;
+              cnt++;
+            }
+          }
+          {
+            const int wc = __reduce_add_sync(0xffffffffu, cnt);
+            const int wt = __any_sync(0xffffffffu, pend != 0);
+            if ((tid & 31) == 0) { int* ip = (int*)&s.red[(tid >> 5) * 10 + 4]; ip[0] = wc; ip[1] = wt; }
+          }
+          block_reduce<4>(s.red, 0, v1, tid);
+          int n = 0, any_tie = 0;
+#pragma unroll
+          for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&s.red[w * 10 + 4]; n += ip[0]; any_tie |= ip[1]; }
+          if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
+            replay_ties(a, s, Rt, m0, nmGA, nmNGA, ns, nsGA, pend, tid);
+            status |= CCICP_ST_TIE_REPLAY;
+            pass1_from_slots(s, Rt, ns, tid, v1[0], v1[1], v1[2], v1[3], cnt);
+            const int wc = __reduce_add_sync(0xffffffffu, cnt);
+            if ((tid & 31) == 0) { int* ip = (int*)&s.red[(tid >> 5) * 10 + 4]; ip[0] = wc; ip[1] = 0; }
+            block_reduce<4>(s.red, 0, v1, tid);
+            n = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; w++) n += ((const int*)&s.red[w * 10 + 4])[0];
+          }
+          iters++;
+          if (n == 0) {                          // fitStep returns -1 before touching R,t (icpPointToPoint.cpp:128-131)
+            last_delta = -1.0; last_failed = true;
+            if (!(-1.0 < a.min_delta)) iters = a.max_iter;   // every remaining fitStep repeats this one
+            break;
+          }
+          last_failed = false; have_ok = true; num_corr = n;
+          // ---- a7: centroids, centred cross-covariance (two-pass like the reference)
+          const double mu_m[2] = {v1[0] / (double)n, v1[1] / (double)n};
+          const double mu_t[2] = {v1[2] / (double)n, v1[3] / (double)n};
+          double H[4] = {0.0, 0.0, 0.0, 0.0};
+          for (int i = tid; i < ns; i += kThreads) {
+            const unsigned slot = s.slots[i];
+            if (slot == kNoSlot) continue;
+            const double2 sp = s.scene[i];
+            float qx, qy;
+            transform(Rt, sp.x, sp.y, qx, qy);
+            const float2 m = s.mpts[slot];
+            const double qm0 = (double)m.x - mu_m[0], qm1 = (double)m.y - mu_m[1];
+            const double qt0 = (double)qx - mu_t[0], qt1 = (double)qy - mu_t[1];
+            H[0] += qt0 * qm0; H[1] += qt0 * qm1; H[2] += qt1 * qm0; H[3] += qt1 * qm1;
+          }
+          block_reduce<4>(s.red, 5, H, tid);
+          if (tid == 0) {
+#pragma unroll
+            for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];
+          }
+          // ---- a8, a9
+          last_delta = solve_and_compose(H, mu_m, mu_t, Rt, status);
+          if (last_delta < a.min_delta) { status |= CCICP_ST_CONVERGED; break; }
+        }
+        if (!have_ok) status |= CCICP_ST_NO_CORR;
+      }
+
+      // ---- outputs: correspondences of the last executed iteration
+      __syncthreads();
+      if (a.corr_idx) {
+        int32_t* dst = a.corr_idx + (size_t)seed * (size_t)a.total_scene + s0;
+        for (int i = tid; i < ns; i += kThreads) {
+          int32_t o = -1;
+          if (model_ok && scene_ok && iters > 0) {
+            const unsigned slot = s.slots[i];
+            if (slot != kNoSlot) o = s.morig[slot];
+          }
+          dst[i] = o;
+        }
+      }
+
+      // ---- score + a10 getEdgeWeight from the last successful iteration's correspondences
+      double info[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      double score = CUDART_INF;
+      if (have_ok) {
+        double P[6];
+#pragma unroll
+        for (int q = 0; q < 6; q++) P[q] = s.rtprev[q];
+        if (last_failed) {       // regenerate the slots of the last successful iteration (ties: grid order)
+          __syncthreads();
+          for (int i = tid; i < ns; i += kThreads) {
+            const double2 sp = s.scene[i];
+            float qx, qy;
+            transform(P, sp.x, sp.y, qx, qy);
+            const GridP& g = s.grid[i >= nsGA];
+            unsigned slot = kNoSlot;
+            if (g.G > 0) {
+              float best; int bslot, tie;
+              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, best, bslot, tie);
+              if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
+            }
+            s.slots[i] = (uint16_t)slot;
+          }
+        }
+        const bool want_info = (a.flags & CCICP_F_INFO) != 0;
+        const bool fixed_dy = (a.flags & CCICP_F_INFO_FIXED_DY) != 0;
+        double v[7] = {0, 0, 0, 0, 0, 0, 0};   // sdis, sx, sy, xpy, mz0, mz1, mz2
+        for (int i = tid; i < ns; i += kThreads) {
+          const unsigned slot = s.slots[i];
+          if (slot == kNoSlot) continue;
+          const double2 sp = s.scene[i];
+          float qx, qy;
+          transform(P, sp.x, sp.y, qx, qy);
+          const float2 m = s.mpts[slot];
+          const float fdx = __fsub_rn(m.x, qx), fdy = __fsub_rn(m.y, qy);
+          v[0] += (double)__fadd_rn(__fmul_rn(fdx, fdx), __fmul_rn(fdy, fdy));
+          if (want_info) {      // icpPointToPoint.cpp:250-275
+            const double ax = (double)m.x, ay = (double)m.y, bx = (double)qx, by = (double)qy;
+            const double x = (ax + bx) / 2.0, y = (ay + by) / 2.0;
+            const double dx = ax - bx, dy = fixed_dy ? ay - by : ax - bx;
+            v[1] += x; v[2] += y; v[3] += x * x + y * y;
+            v[4] += dx; v[5] += dy; v[6] += -y * dx + x * dy;
+          }
+        }
+        block_reduce<7>(s.red, 0, v, tid);
+        const double nn = (double)num_corr;
+        score = v[0] / nn;
+        if (want_info) {
+          // MM = [[n,0,-sy],[0,n,sx],[-sy,sx,xpy]]; D = MM^-1 * MZ (icpPointToPoint.cpp:277-285)
+          const double sx = v[1], sy = v[2], xpy = v[3];
+          const double sch = xpy - (sx * sx + sy * sy) / nn;
+          const double D2 = (v[6] + (sy * v[4] - sx * v[5]) / nn) / sch;
+          const double D0 = (v[4] + sy * D2) / nn, D1 = (v[5] - sx * D2) / nn;
+          double ss[1] = {0.0};
+          __syncthreads();
+          for (int i = tid; i < ns; i += kThreads) {
+            const unsigned slot = s.slots[i];
+            if (slot == kNoSlot) continue;
+            const double2 sp = s.scene[i];
+            float qx, qy;
+            transform(P, sp.x, sp.y, qx, qy);
+            const float2 m = s.mpts[slot];
+            const double ax = (double)m.x, ay = (double)m.y, bx = (double)qx, by = (double)qy;
+            const double x = (ax + bx) / 2.0, y = (ay + by) / 2.0;
+            const double tx = (ax - bx - D0 + y * D2), ty = (ay - by - D1 - x * D2);
+            ss[0] += tx * tx + ty * ty;
+          }
+          block_reduce<1>(s.red, 8, ss, tid);
+          const double sconst = 1.0 / (ss[0] / (double)(2 * num_corr - 3));
+          if (!(sch != 0.0) || !(ss[0] > 0.0)) status |= CCICP_ST_INFO_SINGULAR;
+          info[0] = nn * sconst; info[1] = 0.0 * sconst; info[2] = -sy * sconst;
+          info[3] = 0.0 * sconst; info[4] = nn * sconst; info[5] = sx * sconst;
+          info[6] = -sy * sconst; info[7] = sx * sconst; info[8] = xpy * sconst;
+        }
+      }
+      if (tid == 0) {
+        if (s.misc[M_TREEFAIL]) status |= CCICP_ST_TREE_OVERFLOW;
+        ccicp_result r;
+#pragma unroll
+        for (int q = 0; q < 4; q++) r.R[q] = Rt[q];
+        r.t[0] = Rt[4]; r.t[1] = Rt[5];
+#pragma unroll
+        for (int q = 0; q < 9; q++) r.info[q] = info[q];
+        r.last_delta = last_delta; r.score = score;
+        r.num_corr = num_corr; r.iters = iters; r.status = status; r.best_seed = seed;
+        r.n_tie_replays = s.misc[M_REPLAYS]; r.reserved = 0;
+        a.out[prob] = r;
+      }
+    }
+  }
+}
+
+// best-of-seeds: one warp per pair, arg-min of score over seeds with
+// num_corr >= min_corr_frac * n_scene; ties -> lowest seed index.
+__global__ void select_best_seed_kernel(const ccicp_result* __restrict__ all, ccicp_result* __restrict__ out,
+                                        const int32_t* __restrict__ scene_off, int n_pairs, int n_seeds,
+                                        double min_corr_frac) {
+  const int pair = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (pair >= n_pairs) return;
+  const double need = min_corr_frac * (double)(scene_off[2 * pair + 2] - scene_off[2 * pair]);
+  double best = CUDART_INF;
+  int bseed = 0x7fffffff;
+  for (int sd = lane; sd < n_seeds; sd += 32) {
+    const ccicp_result& r = all[(size_t)pair * n_seeds + sd];
+    double sc = ((double)r.num_corr >= need && r.num_corr > 0) ? r.score : CUDART_INF;
+    if (sc < best) { best = sc; bseed = sd; }      // ascending sd per lane: first minimum kept
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    int os = __shfl_xor_sync(0xffffffffu, bseed, o);
+    if (ob < best || (ob == best && os < bseed)) { best = ob; bseed = os; }
+  }
+  if (bseed == 0x7fffffff) bseed = 0;               // nothing qualified: report seed 0
+  const ccicp_result* src = &all[(size_t)pair * n_seeds + bseed];
+  ccicp_result* dst = &out[pair];
+  const int4* s4 = (const int4*)src;
+  int4* d4 = (int4*)dst;
+  for (int q = lane; q < (int)(sizeof(ccicp_result) / 16); q += 32) d4[q] = s4[q];
+  __syncwarp();
+  if (lane == 0 && !(best < CUDART_INF)) dst->score = CUDART_INF;
+}
+
+}  // namespace ccicp

@@ -1,0 +1,49 @@
+// Host build of the product's tie-replay kd-tree (slam_b200/csrc/kdreplay.h) so
+// its build + traversal can be checked on the CPU against the compiled
+// reference (oracle/_ref) without a GPU.  Test scaffolding only.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+#include "../../slam_b200/csrc/kdreplay.h"
+
+extern "C" {
+
+// Same record layout as oracle/ref_probe.cpp:dump_node (10 floats per node, preorder).
+int kdr_tree(const double* pts, int n, int32_t* ind_out, float* nodes_out, int max_nodes) {
+  std::vector<kdreplay::Pt> p(n > 0 ? n : 1);
+  for (int i = 0; i < n; i++) { p[i].x = (float)pts[2 * i]; p[i].y = (float)pts[2 * i + 1]; }
+  std::vector<kdreplay::Node> nodes(2 * (n > 0 ? n : 1) + 2);
+  int nn = 0;
+  int rc = kdreplay::build(p.data(), n, ind_out, nodes.data(), (int)nodes.size(), &nn);
+  if (rc != kdreplay::OK) return -1000 - rc;
+  if (nn > max_nodes) return -nn;
+  for (int k = 0; k < nn; k++) {
+    const kdreplay::Node& nd = nodes[k];
+    bool leaf = nd.cut_dim < 0;
+    float* r = nodes_out + 10 * k;
+    r[0] = leaf ? -1.0f : (float)nd.cut_dim;
+    r[1] = nd.cut_val;
+    r[2] = leaf ? 0.0f : nd.cut_val_left;
+    r[3] = leaf ? 0.0f : nd.cut_val_right;
+    r[4] = (float)nd.l; r[5] = (float)nd.u;
+    r[6] = nd.box[0]; r[7] = nd.box[1]; r[8] = nd.box[2]; r[9] = nd.box[3];
+  }
+  return nn;
+}
+
+int kdr_nn(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis) {
+  std::vector<kdreplay::Pt> p(n > 0 ? n : 1);
+  for (int i = 0; i < n; i++) { p[i].x = (float)pts[2 * i]; p[i].y = (float)pts[2 * i + 1]; }
+  std::vector<kdreplay::Node> nodes(2 * (n > 0 ? n : 1) + 2);
+  std::vector<int32_t> ind(n > 0 ? n : 1);
+  int nn = 0;
+  int rc = kdreplay::build(p.data(), n, ind.data(), nodes.data(), (int)nodes.size(), &nn);
+  if (rc != kdreplay::OK) return -1000 - rc;
+  for (int i = 0; i < nq; i++) {
+    rc = kdreplay::nearest(p.data(), ind.data(), nodes.data(), nn, q[2 * i], q[2 * i + 1], &idx[i], &dis[i]);
+    if (rc != kdreplay::OK) return -2000 - rc;
+  }
+  return 0;
+}
+
+}
