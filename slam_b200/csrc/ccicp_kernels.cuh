@@ -103,7 +103,7 @@ __host__ __device__ inline size_t smem_bytes(int mcap, int scap, int ccap) {
   return b;
 }
 
-__device__ inline Smem carve(char* base, int mcap, int scap, int ccap) {
+__device__ __forceinline__ Smem carve(char* base, int mcap, int scap, int ccap) {
   Smem s;
   size_t region0 = (size_t)scap * 16;
   size_t need_tmp = (size_t)mcap * 12;
@@ -118,6 +118,10 @@ __device__ inline Smem carve(char* base, int mcap, int scap, int ccap) {
   s.rtprev = (double*)(base + o); o += 8 * 8;
   s.grid = (GridP*)(base + o); o += 2 * sizeof(GridP);
   s.misc = (int*)(base + o);
+  // tell the compiler these are shared-memory addresses so it emits LDS/STS, not generic LD/ST
+  __builtin_assume(__isShared(s.scene)); __builtin_assume(__isShared(s.mpts)); __builtin_assume(__isShared(s.slots));
+  __builtin_assume(__isShared(s.morig)); __builtin_assume(__isShared(s.cstart)); __builtin_assume(__isShared(s.red));
+  __builtin_assume(__isShared(s.rtprev)); __builtin_assume(__isShared(s.grid)); __builtin_assume(__isShared(s.misc));
   return s;
 }
 
@@ -128,61 +132,106 @@ enum { M_WORK = 0, M_BBOX = 1 /* 8 ints: per class minx,miny,maxx,maxy (ordered)
 // ---- exact float nearest neighbour over one class grid ---------------------
 // Returns the float-argmin (identical arithmetic to kdtree.cpp:610-614:
 // dis = fl(fl(dx*dx) + fl(dy*dy)), dx = fl(m - q)), its sorted slot, and
-// whether >= 2 model points share that minimum.  Exact for every point whose
-// dis could pass the gate: the ring walk stops only when a conservative lower
-// bound on the distance of every unvisited cell exceeds min(best, gate).
-__device__ __forceinline__ void scan_slots(const float2* __restrict__ mpts, int s, int e, float qx, float qy,
-                                           float& best, int& bslot, int& tie) {
-  for (int j = s; j < e; j++) {
-    float2 p = mpts[j];
-    float dx = __fsub_rn(p.x, qx);
-    float dy = __fsub_rn(p.y, qy);
-    float d = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-    if (d < best) { best = d; bslot = j; tie = 0; }
-    else if (d == best) tie = 1;
-  }
+// whether >= 2 distinct model points share that minimum.
+//
+// Row sweep in chunks of three grid rows.  An upper bound `best` comes from the
+// previous iteration's match (warm start) or, failing that, from probing the
+// home cell and then the 3x3 block.  A row is cut to the cell span that can
+// still hold a point with dis <= lim = min(best, gate); cells are sorted
+// row-major, so the span is ONE contiguous slot range (2 table reads).  The three
+// ranges of a chunk are walked by one branch-free loop, so the lanes of a warp
+// stay converged.  All bounds are conservative w.r.t. the float arithmetic
+// (slop terms): a point is skipped only if it provably cannot win, tie or pass
+// the gate.
+struct NNQuery {
+  float qx, qy, ux, uy, slop, h, inv_h;
+  int G;
+  const uint16_t* cs;
+};
+
+// slot range of row y that can hold a point within lim of the query, clipped to cells [ca, cb]
+__device__ __forceinline__ void row_span(const NNQuery& q, int y, float lim, int ca, int cb, int& j, int& e) {
+  j = 0; e = 0;
+  if (y < 0 || y >= q.G) return;
+  const float gc = fmaxf(fmaxf((float)y - q.uy, q.uy - (float)(y + 1)), 0.0f) - q.slop;
+  const float gy = fmaxf(gc, 0.0f) * q.h * 0.99999f;
+  const float rem = lim - gy * gy;
+  if (!(rem >= 0.0f)) return;
+  const float su = __fsqrt_ru(rem) * q.inv_h * 1.00001f + q.slop;
+  const int xa = max((int)floorf(q.ux - su), ca), xb = min((int)floorf(q.ux + su), cb);
+  if (xa > xb) return;
+  j = q.cs[y * q.G + xa]; e = q.cs[y * q.G + xb + 1];
+}
+
+__device__ __forceinline__ bool row_reachable(const NNQuery& q, int y, float lim) {
+  if (y < 0 || y >= q.G) return false;
+  const float gc = fmaxf(fmaxf((float)y - q.uy, q.uy - (float)(y + 1)), 0.0f) - q.slop;
+  const float gy = fmaxf(gc, 0.0f) * q.h * 0.99999f;
+  return gy * gy <= lim;
 }
 
 __device__ __forceinline__ void nn_search(const float2* __restrict__ mpts, const uint16_t* __restrict__ cstart,
-                                          const GridP& g, float qx, float qy, float gate_f,
+                                          const GridP& g, float qx, float qy, float gate_f, unsigned warm,
                                           float& best, int& bslot, int& tie) {
   best = CUDART_INF_F; bslot = -1; tie = 0;
+  NNQuery q;
+  q.qx = qx; q.qy = qy; q.G = g.G; q.h = g.h; q.inv_h = g.inv_h; q.cs = cstart + g.base;
+  q.ux = fminf(fmaxf(__fmul_rn(__fsub_rn(qx, g.minx), g.inv_h), -1.0e6f), 1.0e6f);
+  q.uy = fminf(fmaxf(__fmul_rn(__fsub_rn(qy, g.miny), g.inv_h), -1.0e6f), 1.0e6f);
+  q.slop = 0.01f + 4e-7f * fmaxf(fabsf(q.ux), fabsf(q.uy));
   const int G = g.G;
-  float ux = __fmul_rn(__fsub_rn(qx, g.minx), g.inv_h);
-  float uy = __fmul_rn(__fsub_rn(qy, g.miny), g.inv_h);
-  ux = fminf(fmaxf(ux, -1.0e6f), 1.0e6f);
-  uy = fminf(fmaxf(uy, -1.0e6f), 1.0e6f);
-  const float fxl = floorf(ux), fyl = floorf(uy);
-  const int cx = (int)fxl, cy = (int)fyl;
-  const float fx = ux - fxl, fy = uy - fyl;
-  const float m = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
-  const float slop = 0.01f + 4e-7f * fmaxf(fabsf(ux), fabsf(uy));
-  int r0 = max(max(-cx, cx - (G - 1)), max(-cy, cy - (G - 1)));
-  r0 = max(r0, 0);
-  const int rend = max(max(cx, G - 1 - cx), max(cy, G - 1 - cy));
-  const uint16_t* cs = cstart + g.base;
-  for (int r = r0; r <= rend; r++) {
-    if (r > 0) {
-      float lbc = (float)(r - 1) + m - slop;
-      if (lbc > 0.0f) {
-        float lb = lbc * g.h * 0.99999f;
-        if (lb * lb > fminf(best, gate_f)) break;
-      }
+  const int cx = (int)floorf(q.ux), cy = (int)floorf(q.uy);
+  const int cyc = min(max(cy, 0), G - 1);
+  // phase A: an upper bound B on the answer (warm start, else probes).  Phase B then sweeps from scratch
+  // with best just above B, so every point is tested exactly once there and ties need no slot compare.
+  int stage = 0;          // 0 probe home cell, 1 probe 3x3, 2 centre rows, 3 rows below, 4 rows above
+  if (warm != kNoSlot) {
+    const float2 p = mpts[warm];
+    const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+    best = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+    stage = 2;
+  }
+  int yd = cyc - 2, yu = cyc + 2;
+  for (;;) {
+    int y0, ca = 0, cb = G - 1, dir = 1;
+    bool only_mid = false;
+    if (stage == 0) { y0 = cy - 1; ca = max(cx, 0); cb = min(cx, G - 1); only_mid = true; stage = 1; }
+    else if (stage == 1) {
+      stage = 2;
+      if (best < CUDART_INF_F) continue;
+      y0 = cy - 1; ca = max(cx - 1, 0); cb = min(cx + 1, G - 1);
     }
-    const int xa = max(cx - r, 0), xb = min(cx + r, G - 1);
-    const int ya = cy - r, yb = cy + r;
-    if (xa <= xb) {
-      if (ya >= 0 && ya < G) scan_slots(mpts, cs[ya * G + xa], cs[ya * G + xb + 1], qx, qy, best, bslot, tie);
-      if (r > 0 && yb >= 0 && yb < G) scan_slots(mpts, cs[yb * G + xa], cs[yb * G + xb + 1], qx, qy, best, bslot, tie);
+    else if (stage == 2) {               // start of the exact sweep: keep only the bound
+      best = __int_as_float(__float_as_int(best) + (best < CUDART_INF_F ? 1 : 0));   // next float above B (B >= 0)
+      bslot = -1; tie = 0;
+      y0 = cyc - 1; stage = 3;
     }
-    if (r > 0) {
-      const int y0 = max(ya + 1, 0), y1 = min(yb - 1, G - 1);
-      const int xl = cx - r, xr = cx + r;
-      const bool hl = xl >= 0 && xl < G, hr = xr >= 0 && xr < G;
-      for (int y = y0; y <= y1; y++) {
-        if (hl) scan_slots(mpts, cs[y * G + xl], cs[y * G + xl + 1], qx, qy, best, bslot, tie);
-        if (hr) scan_slots(mpts, cs[y * G + xr], cs[y * G + xr + 1], qx, qy, best, bslot, tie);
-      }
+    else if (stage == 3) {
+      if (!row_reachable(q, yd, fminf(best, gate_f))) { stage = 4; continue; }
+      y0 = yd; dir = -1; yd -= 3;
+    } else {
+      if (!row_reachable(q, yu, fminf(best, gate_f))) break;
+      y0 = yu; yu += 3;
+    }
+    const float lim = fminf(best, gate_f);
+    int j0, e0, j1, e1, j2, e2;
+    row_span(q, only_mid ? -1 : y0, lim, ca, cb, j0, e0);
+    row_span(q, y0 + dir, lim, ca, cb, j1, e1);
+    row_span(q, only_mid ? -1 : y0 + 2 * dir, lim, ca, cb, j2, e2);
+    const int n0 = e0 - j0, n01 = n0 + (e1 - j1), tot = n01 + (e2 - j2);
+    const int o1 = j1 - n0, o2 = j2 - n01;
+#pragma unroll 2
+    for (int t = 0; t < tot; t++) {
+      int off = o2;
+      off = t < n01 ? o1 : off;
+      off = t < n0 ? j0 : off;
+      const int j = t + off;
+      const float2 p = mpts[j];
+      const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+      const float d = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+      tie = d < best ? 0 : (d == best ? 1 : tie);
+      bslot = d < best ? j : bslot;
+      best = fminf(best, d);
     }
   }
 }

@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
       bool have_ok = false, last_failed = false;
       __syncthreads();
       if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; }
+      for (int i = tid; i < ns; i += kThreads) s.slots[i] = (uint16_t)kNoSlot;   // no warm start for a new seed
 
       if (!model_ok) status |= CCICP_ST_TOO_FEW_MODEL;
       else if (!scene_ok) status |= CCICP_ST_TOO_FEW_SCENE;
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, best, bslot, tie);
+              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, s.slots[i], best, bslot, tie);
               if (bslot >= 0 && (double)best < a.indist) {
                 slot = (unsigned)bslot;
                 if (tie && replay_on) pend |= 1u << (k & 31);
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, best, bslot, tie);
+              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie);
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
             }
             s.slots[i] = (uint16_t)slot;
