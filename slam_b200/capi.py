@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libccicp2d_b200.so")
+LIB_PATH = os.environ.get("CCICP_LIB") or os.path.join(_HERE, "lib", "libccicp2d_b200.so")
 
 # error codes / status bits / flags (mirror the header)
 OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)

@@ -30,6 +30,7 @@ constexpr unsigned kNoSlot = 0xFFFFu;
 
 struct GridP {          // per class
   float minx, miny, inv_h, h;
+  float cx, cy; int32_t pad0, pad1;   // bbox centre: pivot of the shifted sums
   int32_t G, base, n, first;   // cells per side, first cell id, model points, first model point (class offset)
 };
 
@@ -80,7 +81,7 @@ struct Smem {
   uint16_t* slots;     // [scap]   matched sorted-slot per scene point, kNoSlot = none
   uint16_t* morig;     // [mcap]   sorted slot -> per-class original model index
   uint16_t* cstart;    // [ccap+2] cell -> first sorted slot (exclusive prefix), packed counters while building
-  double* red;         // [kWarps*10]
+  double* red;         // [2][kWarps*10] double-buffered by iteration parity
   double* rtprev;      // [8] pre-update R,t of the last successful iteration
   GridP* grid;         // [2]
   int* misc;           // [16]
@@ -97,7 +98,7 @@ __host__ __device__ inline size_t smem_bytes(int mcap, int scap, int ccap) {
   b += align_up((size_t)scap * 2, 16);
   b += align_up((size_t)mcap * 2, 16);
   b += align_up((size_t)(ccap + 4) * 2, 16);
-  b += (kWarps * 10 + 8) * 8;
+  b += (2 * kWarps * 10 + 8) * 8;
   b += 2 * sizeof(GridP);
   b += 16 * 4;
   return b;
@@ -114,7 +115,7 @@ __device__ __forceinline__ Smem carve(char* base, int mcap, int scap, int ccap) 
   s.slots = (uint16_t*)(base + o); o += align_up((size_t)scap * 2, 16);
   s.morig = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
   s.cstart = (uint16_t*)(base + o); o += align_up((size_t)(ccap + 4) * 2, 16);
-  s.red = (double*)(base + o); o += kWarps * 10 * 8;
+  s.red = (double*)(base + o); o += 2 * kWarps * 10 * 8;
   s.rtprev = (double*)(base + o); o += 8 * 8;
   s.grid = (GridP*)(base + o); o += 2 * sizeof(GridP);
   s.misc = (int*)(base + o);
@@ -149,91 +150,74 @@ struct NNQuery {
   const uint16_t* cs;
 };
 
-// slot range of row y that can hold a point within lim of the query, clipped to cells [ca, cb]
-__device__ __forceinline__ void row_span(const NNQuery& q, int y, float lim, int ca, int cb, int& j, int& e) {
-  j = 0; e = 0;
-  if (y < 0 || y >= q.G) return;
-  const float gc = fmaxf(fmaxf((float)y - q.uy, q.uy - (float)(y + 1)), 0.0f) - q.slop;
-  const float gy = fmaxf(gc, 0.0f) * q.h * 0.99999f;
-  const float rem = lim - gy * gy;
-  if (!(rem >= 0.0f)) return;
-  const float su = __fsqrt_ru(rem) * q.inv_h * 1.00001f + q.slop;
-  const int xa = max((int)floorf(q.ux - su), ca), xb = min((int)floorf(q.ux + su), cb);
-  if (xa > xb) return;
-  j = q.cs[y * q.G + xa]; e = q.cs[y * q.G + xb + 1];
-}
-
-__device__ __forceinline__ bool row_reachable(const NNQuery& q, int y, float lim) {
-  if (y < 0 || y >= q.G) return false;
-  const float gc = fmaxf(fmaxf((float)y - q.uy, q.uy - (float)(y + 1)), 0.0f) - q.slop;
-  const float gy = fmaxf(gc, 0.0f) * q.h * 0.99999f;
-  return gy * gy <= lim;
-}
-
 __device__ __forceinline__ void nn_search(const float2* __restrict__ mpts, const uint16_t* __restrict__ cstart,
                                           const GridP& g, float qx, float qy, float gate_f, unsigned warm,
                                           float& best, int& bslot, int& tie) {
-  best = CUDART_INF_F; bslot = -1; tie = 0;
-  NNQuery q;
-  q.qx = qx; q.qy = qy; q.G = g.G; q.h = g.h; q.inv_h = g.inv_h; q.cs = cstart + g.base;
-  q.ux = fminf(fmaxf(__fmul_rn(__fsub_rn(qx, g.minx), g.inv_h), -1.0e6f), 1.0e6f);
-  q.uy = fminf(fmaxf(__fmul_rn(__fsub_rn(qy, g.miny), g.inv_h), -1.0e6f), 1.0e6f);
-  q.slop = 0.01f + 4e-7f * fmaxf(fabsf(q.ux), fabsf(q.uy));
+  best = CUDART_INF_F; bslot = -1;
+  float second = CUDART_INF_F;      // second smallest distance seen (with multiplicity): tie <=> second == best
   const int G = g.G;
-  const int cx = (int)floorf(q.ux), cy = (int)floorf(q.uy);
-  const int cyc = min(max(cy, 0), G - 1);
-  // phase A: an upper bound B on the answer (warm start, else probes).  Phase B then sweeps from scratch
-  // with best just above B, so every point is tested exactly once there and ties need no slot compare.
-  int stage = 0;          // 0 probe home cell, 1 probe 3x3, 2 centre rows, 3 rows below, 4 rows above
+  const float inv_h = g.inv_h;
+  const uint16_t* cs = cstart + g.base;
+  const float ux = fminf(fmaxf(__fmul_rn(__fsub_rn(qx, g.minx), inv_h), -1.0e6f), 1.0e6f);
+  const float uy = fminf(fmaxf(__fmul_rn(__fsub_rn(qy, g.miny), inv_h), -1.0e6f), 1.0e6f);
+  const float slop = 0.01f + 4e-7f * fmaxf(fabsf(ux), fabsf(uy));
+  // task 0: probe the home cell, 1: probe the 3x3 block (both only to get an upper bound B when there is no
+  // warm start), 2: exact sweep of every cell that can hold a point with dis <= min(B+, gate).
+  int task = 0;
   if (warm != kNoSlot) {
     const float2 p = mpts[warm];
     const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
     best = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-    stage = 2;
+    task = 2;
   }
-  int yd = cyc - 2, yu = cyc + 2;
   for (;;) {
-    int y0, ca = 0, cb = G - 1, dir = 1;
-    bool only_mid = false;
-    if (stage == 0) { y0 = cy - 1; ca = max(cx, 0); cb = min(cx, G - 1); only_mid = true; stage = 1; }
-    else if (stage == 1) {
-      stage = 2;
-      if (best < CUDART_INF_F) continue;
-      y0 = cy - 1; ca = max(cx - 1, 0); cb = min(cx + 1, G - 1);
-    }
-    else if (stage == 2) {               // start of the exact sweep: keep only the bound
-      best = __int_as_float(__float_as_int(best) + (best < CUDART_INF_F ? 1 : 0));   // next float above B (B >= 0)
-      bslot = -1; tie = 0;
-      y0 = cyc - 1; stage = 3;
-    }
-    else if (stage == 3) {
-      if (!row_reachable(q, yd, fminf(best, gate_f))) { stage = 4; continue; }
-      y0 = yd; dir = -1; yd -= 3;
+    int xa, xb, ya, yb;
+    if (task < 2) {
+      if (task == 1 && best < CUDART_INF_F) { task = 2; continue; }
+      const int cx = (int)floorf(ux), cy = (int)floorf(uy);
+      xa = cx - task; xb = cx + task; ya = cy - task; yb = cy + task;
     } else {
-      if (!row_reachable(q, yu, fminf(best, gate_f))) break;
-      y0 = yu; yu += 3;
+      // keep only the bound: restart from the next float above B so every point is tested exactly once
+      best = __int_as_float(__float_as_int(best) + (best < CUDART_INF_F ? 1 : 0));
+      second = CUDART_INF_F; bslot = -1;
+      const float su = __fsqrt_ru(fminf(best, gate_f)) * inv_h * 1.00001f + slop;   // search radius in cells, rounded up
+      xa = (int)floorf(ux - su); xb = (int)floorf(ux + su);
+      ya = (int)floorf(uy - su); yb = (int)floorf(uy + su);
     }
-    const float lim = fminf(best, gate_f);
-    int j0, e0, j1, e1, j2, e2;
-    row_span(q, only_mid ? -1 : y0, lim, ca, cb, j0, e0);
-    row_span(q, y0 + dir, lim, ca, cb, j1, e1);
-    row_span(q, only_mid ? -1 : y0 + 2 * dir, lim, ca, cb, j2, e2);
-    const int n0 = e0 - j0, n01 = n0 + (e1 - j1), tot = n01 + (e2 - j2);
-    const int o1 = j1 - n0, o2 = j2 - n01;
+    xa = max(xa, 0); xb = min(xb, G - 1); ya = max(ya, 0); yb = min(yb, G - 1);
+    if (xa <= xb) {
+      for (int y = ya; y <= yb; y += 3) {
+        if (y > ya) {                       // later chunks: shrink the column span to the current bound
+          const float su = __fsqrt_ru(fminf(best, gate_f)) * inv_h * 1.00001f + slop;
+          xa = max(xa, (int)floorf(ux - su)); xb = min(xb, (int)floorf(ux + su));
+          if (xa > xb) break;
+        }
+        const uint16_t* r0 = cs + y * G;
+        const int j0 = r0[xa], e0 = r0[xb + 1];
+        int j1 = 0, e1 = 0, j2 = 0, e2 = 0;
+        if (y + 1 <= yb) { j1 = r0[G + xa]; e1 = r0[G + xb + 1]; }
+        if (y + 2 <= yb) { j2 = r0[2 * G + xa]; e2 = r0[2 * G + xb + 1]; }
+        const int n0 = e0 - j0, n01 = n0 + (e1 - j1), tot = n01 + (e2 - j2);
+        const int o1 = j1 - n0, o2 = j2 - n01;
 #pragma unroll 2
-    for (int t = 0; t < tot; t++) {
-      int off = o2;
-      off = t < n01 ? o1 : off;
-      off = t < n0 ? j0 : off;
-      const int j = t + off;
-      const float2 p = mpts[j];
-      const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
-      const float d = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-      tie = d < best ? 0 : (d == best ? 1 : tie);
-      bslot = d < best ? j : bslot;
-      best = fminf(best, d);
+        for (int t = 0; t < tot; t++) {
+          int off = o2;
+          off = t < n01 ? o1 : off;
+          off = t < n0 ? j0 : off;
+          const int j = t + off;
+          const float2 p = mpts[j];
+          const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+          const float d = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+          bslot = d < best ? j : bslot;
+          second = fminf(second, fmaxf(d, best));
+          best = fminf(best, d);
+        }
+      }
     }
+    if (task == 2) break;
+    task++;
   }
+  tie = (bslot >= 0 && second == best) ? 1 : 0;
 }
 
 // a4: q = float((r00*x + r01*y) + t0), FP64 un-fused (icpPointToPoint.cpp:69-70)

@@ -47,13 +47,14 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
     g.base = tid ? G0 * G0 : 0;
     g.n = n;
     g.first = tid ? nGA : 0;
-    g.minx = g.miny = 0.0f; g.h = 1.0f; g.inv_h = 1.0f;
+    g.minx = g.miny = 0.0f; g.h = 1.0f; g.inv_h = 1.0f; g.cx = g.cy = 0.0f; g.pad0 = g.pad1 = 0;
     if (g.G > 0) {
       const float minx = ord2f(s.misc[M_BBOX + 4 * tid + 0]), miny = ord2f(s.misc[M_BBOX + 4 * tid + 1]);
       const float maxx = ord2f(s.misc[M_BBOX + 4 * tid + 2]), maxy = ord2f(s.misc[M_BBOX + 4 * tid + 3]);
       float ext = fmaxf(maxx - minx, maxy - miny);
       if (!(ext > 1.0e-6f)) ext = 1.0e-6f;
       g.minx = minx; g.miny = miny;
+      g.cx = 0.5f * minx + 0.5f * maxx; g.cy = 0.5f * miny + 0.5f * maxy;
       g.h = ext / (float)g.G;
       g.inv_h = (float)g.G / ext;
     }
@@ -177,18 +178,32 @@ __device__ __noinline__ void replay_ties(const IcpArgs& a, const Smem& s, const 
   __syncthreads();
 }
 
-// pass-1 partial sums recomputed from slots[] (used after a tie replay)
-__device__ __forceinline__ void pass1_from_slots(const Smem& s, const double* Rt, int ns, int tid,
-                                                 double& smx, double& smy, double& stx, double& sty, int& cnt) {
-  smx = smy = stx = sty = 0.0; cnt = 0;
+// Shifted one-pass statistics (a7).  With pivot c (centre of the model's bounding box) every thread
+// accumulates  S_m = sum(m - c), S_t = sum(q - c), P = sum (q - c)(m - c)^T ; then
+//   mu_m = c + S_m/n, mu_t = c + S_t/n, H = P - n (S_t/n)(S_m/n)^T
+// which equals the reference's centred H = sum (q - mu_t)(m - mu_m)^T (icpPointToPoint.cpp:149-159) in exact
+// arithmetic and differs from its sequential FP64 evaluation only by rounding (~1e-16 relative).
+__device__ __forceinline__ void accum_corr(double (&v)[8], const float2 m, float qx, float qy, double pcx, double pcy) {
+  const double m0 = (double)m.x - pcx, m1 = (double)m.y - pcy;
+  const double t0 = (double)qx - pcx, t1 = (double)qy - pcy;
+  v[0] += m0; v[1] += m1; v[2] += t0; v[3] += t1;
+  v[4] += t0 * m0; v[5] += t0 * m1; v[6] += t1 * m0; v[7] += t1 * m1;
+}
+
+// partial sums recomputed from slots[] (used after a tie replay)
+__device__ __forceinline__ void sums_from_slots(const Smem& s, const double* Rt, int ns, int tid, double pcx, double pcy,
+                                                double (&v)[8], int& cnt) {
+#pragma unroll
+  for (int k = 0; k < 8; k++) v[k] = 0.0;
+  cnt = 0;
   for (int i = tid; i < ns; i += kThreads) {
     const unsigned slot = s.slots[i];
     if (slot == kNoSlot) continue;
     double2 sp = s.scene[i];
     float qx, qy;
     transform(Rt, sp.x, sp.y, qx, qy);
-    float2 m = s.mpts[slot];
-    smx += (double)m.x; smy += (double)m.y; stx += (double)qx; sty += (double)qy; cnt++;
+    accum_corr(v, s.mpts[slot], qx, qy, pcx, pcy);
+    cnt++;
   }
 }
 

@@ -106,13 +106,14 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
       if (!model_ok) status |= CCICP_ST_TOO_FEW_MODEL;
       else if (!scene_ok) status |= CCICP_ST_TOO_FEW_SCENE;
       else {
+        const GridP& gp = s.grid[nmNGA >= nmGA];
+        const double pcx = (double)gp.cx, pcy = (double)gp.cy;     // pivot of the shifted sums
         for (int iter = 0; iter < a.max_iter; iter++) {
-          // ---- a4..a6: transform, nearest neighbour, gate; pass-1 partial sums
-          double v1[4] = {0.0, 0.0, 0.0, 0.0};
-          int cnt = 0;
+          double* red = s.red + (iter & 1) * (kWarps * 10);
+          // ---- a4..a6: transform, nearest neighbour, gate; shifted sums of the accepted pairs
           uint32_t pend = 0;
           int k = 0;
-          for (int i = tid; i < ns; i += kThreads, k++) {
+          for (int i = tid; i < ns; i += kThreads, k++) {          // loop A: search only (few live registers)
             const double2 sp = s.scene[i];
             float qx, qy;
             transform(Rt, sp.x, sp.y, qx, qy);
@@ -127,31 +128,29 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
               }
             }
             s.slots[i] = (uint16_t)slot;
-            if (slot != kNoSlot) {
-              const float2 m = s.mpts[slot];
-              v1[0] += (double)m.x; v1[1] += (double)m.y; v1[2] += (double)qx; v1[3] += (double)qy;
-              cnt++;
-            }
           }
+          double v[8];
+          int cnt;
+          sums_from_slots(s, Rt, ns, tid, pcx, pcy, v, cnt);        // loop B: converged accumulation
           {
             const int wc = __reduce_add_sync(0xffffffffu, cnt);
             const int wt = __any_sync(0xffffffffu, pend != 0);
-            if ((tid & 31) == 0) { int* ip = (int*)&s.red[(tid >> 5) * 10 + 4]; ip[0] = wc; ip[1] = wt; }
+            if ((tid & 31) == 0) { int* ip = (int*)&red[(tid >> 5) * 10 + 8]; ip[0] = wc; ip[1] = wt; }
           }
-          block_reduce<4>(s.red, 0, v1, tid);
+          block_reduce<8>(red, 0, v, tid);
           int n = 0, any_tie = 0;
 #pragma unroll
-          for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&s.red[w * 10 + 4]; n += ip[0]; any_tie |= ip[1]; }
+          for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&red[w * 10 + 8]; n += ip[0]; any_tie |= ip[1]; }
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
             replay_ties(a, s, Rt, m0, nmGA, nmNGA, ns, nsGA, pend, tid);
             status |= CCICP_ST_TIE_REPLAY;
-            pass1_from_slots(s, Rt, ns, tid, v1[0], v1[1], v1[2], v1[3], cnt);
+            sums_from_slots(s, Rt, ns, tid, pcx, pcy, v, cnt);
             const int wc = __reduce_add_sync(0xffffffffu, cnt);
-            if ((tid & 31) == 0) { int* ip = (int*)&s.red[(tid >> 5) * 10 + 4]; ip[0] = wc; ip[1] = 0; }
-            block_reduce<4>(s.red, 0, v1, tid);
+            if ((tid & 31) == 0) { int* ip = (int*)&red[(tid >> 5) * 10 + 8]; ip[0] = wc; ip[1] = 0; }
+            block_reduce<8>(red, 0, v, tid);
             n = 0;
 #pragma unroll
-            for (int w = 0; w < kWarps; w++) n += ((const int*)&s.red[w * 10 + 4])[0];
+            for (int w = 0; w < kWarps; w++) n += ((const int*)&red[w * 10 + 8])[0];
           }
           iters++;
           if (n == 0) {                          // fitStep returns -1 before touching R,t (icpPointToPoint.cpp:128-131)
@@ -160,22 +159,13 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
             break;
           }
           last_failed = false; have_ok = true; num_corr = n;
-          // ---- a7: centroids, centred cross-covariance (two-pass like the reference)
-          const double mu_m[2] = {v1[0] / (double)n, v1[1] / (double)n};
-          const double mu_t[2] = {v1[2] / (double)n, v1[3] / (double)n};
-          double H[4] = {0.0, 0.0, 0.0, 0.0};
-          for (int i = tid; i < ns; i += kThreads) {
-            const unsigned slot = s.slots[i];
-            if (slot == kNoSlot) continue;
-            const double2 sp = s.scene[i];
-            float qx, qy;
-            transform(Rt, sp.x, sp.y, qx, qy);
-            const float2 m = s.mpts[slot];
-            const double qm0 = (double)m.x - mu_m[0], qm1 = (double)m.y - mu_m[1];
-            const double qt0 = (double)qx - mu_t[0], qt1 = (double)qy - mu_t[1];
-            H[0] += qt0 * qm0; H[1] += qt0 * qm1; H[2] += qt1 * qm0; H[3] += qt1 * qm1;
-          }
-          block_reduce<4>(s.red, 5, H, tid);
+          // ---- a7: centroids and centred cross-covariance from the shifted sums
+          const double inv_n = 1.0 / (double)n;
+          const double dm0 = v[0] / (double)n, dm1 = v[1] / (double)n, dt0 = v[2] / (double)n, dt1 = v[3] / (double)n;
+          const double mu_m[2] = {pcx + dm0, pcy + dm1};
+          const double mu_t[2] = {pcx + dt0, pcy + dt1};
+          (void)inv_n;
+          const double H[4] = {v[4] - v[2] * dm0, v[5] - v[2] * dm1, v[6] - v[3] * dm0, v[7] - v[3] * dm1};
           if (tid == 0) {
 #pragma unroll
             for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];
