@@ -22,6 +22,10 @@
 #include "../../include/ccicp2d_b200.h"
 #include "kdreplay.h"
 
+#ifndef CCICP_GBIG
+#define CCICP_GBIG 64      // cells per side for classes with > 512 model points
+#endif
+
 namespace ccicp {
 
 constexpr int kThreads = 256;
@@ -57,7 +61,7 @@ __host__ __device__ inline int grid_side(int n) {
   if (n <= 32) return 8;
   if (n <= 128) return 16;
   if (n <= 512) return 32;
-  return 64;
+  return CCICP_GBIG;
 }
 
 __device__ __forceinline__ int f2ord(float f) {   // monotone float -> int
@@ -80,7 +84,10 @@ struct Smem {
   float2* mpts;        // [mcap]   model points, float, sorted by cell
   uint16_t* slots;     // [scap]   matched sorted-slot per scene point, kNoSlot = none
   uint16_t* morig;     // [mcap]   sorted slot -> per-class original model index
+  uint16_t* kinv;      // [mcap]   original model index (GA block then NGA block) -> sorted slot
+  uint16_t* kind;      // [mcap]   tie replay: the reference kd-tree's index permutation (built lazily)
   uint16_t* cstart;    // [ccap+2] cell -> first sorted slot (exclusive prefix), packed counters while building
+  uint32_t* tiebits;   // [scap/32] scene points whose float minimum is shared (tie replay work list)
   double* red;         // [2][kWarps*10] double-buffered by iteration parity
   double* rtprev;      // [8] pre-update R,t of the last successful iteration
   GridP* grid;         // [2]
@@ -96,8 +103,9 @@ __host__ __device__ inline size_t smem_bytes(int mcap, int scap, int ccap) {
   size_t b = align_up(region0, 16);
   b += align_up((size_t)mcap * 8, 16);
   b += align_up((size_t)scap * 2, 16);
-  b += align_up((size_t)mcap * 2, 16);
+  b += 3 * align_up((size_t)mcap * 2, 16);
   b += align_up((size_t)(ccap + 4) * 2, 16);
+  b += align_up((size_t)(scap / 32 + 1) * 4, 16);
   b += (2 * kWarps * 10 + 8) * 8;
   b += 2 * sizeof(GridP);
   b += 16 * 4;
@@ -114,14 +122,17 @@ __device__ __forceinline__ Smem carve(char* base, int mcap, int scap, int ccap) 
   s.mpts = (float2*)(base + o); o += align_up((size_t)mcap * 8, 16);
   s.slots = (uint16_t*)(base + o); o += align_up((size_t)scap * 2, 16);
   s.morig = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
+  s.kinv = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
+  s.kind = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
   s.cstart = (uint16_t*)(base + o); o += align_up((size_t)(ccap + 4) * 2, 16);
+  s.tiebits = (uint32_t*)(base + o); o += align_up((size_t)(scap / 32 + 1) * 4, 16);
   s.red = (double*)(base + o); o += 2 * kWarps * 10 * 8;
   s.rtprev = (double*)(base + o); o += 8 * 8;
   s.grid = (GridP*)(base + o); o += 2 * sizeof(GridP);
   s.misc = (int*)(base + o);
   // tell the compiler these are shared-memory addresses so it emits LDS/STS, not generic LD/ST
   __builtin_assume(__isShared(s.scene)); __builtin_assume(__isShared(s.mpts)); __builtin_assume(__isShared(s.slots));
-  __builtin_assume(__isShared(s.morig)); __builtin_assume(__isShared(s.cstart)); __builtin_assume(__isShared(s.red));
+  __builtin_assume(__isShared(s.morig)); __builtin_assume(__isShared(s.kinv)); __builtin_assume(__isShared(s.kind)); __builtin_assume(__isShared(s.cstart)); __builtin_assume(__isShared(s.red)); __builtin_assume(__isShared(s.tiebits));
   __builtin_assume(__isShared(s.rtprev)); __builtin_assume(__isShared(s.grid)); __builtin_assume(__isShared(s.misc));
   return s;
 }

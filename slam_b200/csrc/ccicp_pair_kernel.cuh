@@ -107,74 +107,67 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
     const int slot = s.cstart[tmp_cell[i]] + tmp_rank[i];
     s.mpts[slot] = tmp_pts[i];
     s.morig[slot] = (uint16_t)(i - (cls ? nGA : 0));
+    s.kinv[i] = (uint16_t)slot;
   }
   __syncthreads();
 }
 
 // ---- tie replay (rare): rebuild the reference kd-tree, re-answer tied queries
-struct ReplayScratch { kdreplay::Pt* pts; int32_t* ind; kdreplay::Node* nodes; };
+// The build is the reference's sequential algorithm (float mean split, in-order partition), so it runs on
+// one thread per class; its working set (points via kinv -> mpts, permutation kind) lives in shared memory
+// and only the node records go to a per-CTA global scratch.
+struct SmemPts {
+  const float2* mpts; const uint16_t* inv;
+  __device__ __forceinline__ kdreplay::Pt operator()(int i) const {
+    const float2 v = mpts[inv[i]];
+    kdreplay::Pt p; p.x = v.x; p.y = v.y;
+    return p;
+  }
+};
 
-__device__ __forceinline__ ReplayScratch replay_scratch(const IcpArgs& a) {
-  char* base = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta;
-  ReplayScratch r;
-  r.nodes = (kdreplay::Node*)base;
-  base += align_up((size_t)(2 * a.max_model + 8) * sizeof(kdreplay::Node), 16);
-  r.pts = (kdreplay::Pt*)base;
-  base += align_up((size_t)a.max_model * sizeof(kdreplay::Pt), 16);
-  r.ind = (int32_t*)base;
-  return r;
-}
 __host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
-  return align_up((size_t)(2 * max_model + 8) * sizeof(kdreplay::Node), 16) +
-         align_up((size_t)max_model * sizeof(kdreplay::Pt), 16) + align_up((size_t)max_model * 4, 16);
+  return align_up((size_t)(2 * max_model + 16) * sizeof(kdreplay::LNode), 16);
 }
 
-__device__ __noinline__ void replay_ties(const IcpArgs& a, const Smem& s, const double* Rt, int m0, int nGA, int nNGA,
-                                         int ns, int nsGA, uint32_t pend, int tid) {
-  const int nm = nGA + nNGA;
-  ReplayScratch rs = replay_scratch(a);
-  const bool need_build = (s.grid[0].G > 0 && s.misc[M_TREE + 0] == 0) || (s.grid[1].G > 0 && s.misc[M_TREE + 1] == 0);
+// Tied queries are listed in s.tiebits.  Thread c (c = 0 GA, 1 NGA) replays the tied queries of its class one
+// after the other on the class's lazily materialised reference kd-tree (kdreplay.h): the partition work is
+// sequential by definition, and ties are rare (about 1e-7 per query on scan data), so latency is what counts.
+__device__ __noinline__ void replay_ties(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid) {
   __syncthreads();
-  if (need_build) {
-    const double2* src = (const double2*)a.model_xy + m0;
-    for (int i = tid; i < nm; i += kThreads) {
-      double2 p = src[i];
-      rs.pts[i].x = __double2float_rn(p.x); rs.pts[i].y = __double2float_rn(p.y);
+  if (tid < 2 && s.grid[tid].G > 0) {
+    const GridP g = s.grid[tid];
+    kdreplay::LNode* nodes = (kdreplay::LNode*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta) + 2 * g.first + 8 * tid;
+    const int max_nodes = 2 * g.n + 8;
+    const SmemPts pts{s.mpts, s.kinv + g.first};
+    uint16_t* ind = s.kind + g.first;
+    int nn = s.misc[M_NNODE + tid];
+    int state = s.misc[M_TREE + tid];
+    const int i0 = tid ? nsGA : 0, i1 = tid ? ns : nsGA;
+    for (int w = i0 >> 5; w <= (i1 - 1) >> 5 && i1 > i0; w++) {
+      uint32_t bits = s.tiebits[w];
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int i = (w << 5) + b;
+        if (i < i0 || i >= i1) continue;
+        if (state == 0) state = (kdreplay::lazy_init(pts, g.n, ind, nodes, &nn) == kdreplay::OK) ? 1 : 2;
+        if (state != 1) continue;                  // tree unavailable: keep the grid's answer
+        const double2 sp = s.scene[i];
+        float qx, qy;
+        transform(Rt, sp.x, sp.y, qx, qy);
+        int32_t o = -1; float d = 0.0f;
+        const int rc = kdreplay::lazy_nearest(pts, ind, nodes, max_nodes, &nn, qx, qy, &o, &d);
+        if (rc != kdreplay::OK || o < 0) { state = 2; continue; }
+        s.slots[i] = s.kinv[g.first + o];
+        atomicAdd(&s.misc[M_REPLAYS], 1);
+      }
     }
-    __syncthreads();
-    if (tid < 2 && s.grid[tid].G > 0 && s.misc[M_TREE + tid] == 0) {      // one thread per class
-      const int first = s.grid[tid].first, n = s.grid[tid].n;
-      int nn = 0;
-      int rc = kdreplay::build(rs.pts + first, n, rs.ind + first, rs.nodes + 2 * first + 4 * tid, 2 * n + 4, &nn);
-      s.misc[M_NNODE + tid] = nn;
-      s.misc[M_TREE + tid] = (rc == kdreplay::OK) ? 1 : 2;
-      if (rc != kdreplay::OK) atomicOr(&s.misc[M_TREEFAIL], 1);
-    }
-    __syncthreads();
+    s.misc[M_NNODE + tid] = nn;
+    s.misc[M_TREE + tid] = state;
+    if (state == 2) atomicOr(&s.misc[M_TREEFAIL], 1);
   }
-  int k = 0;
-  for (int i = tid; i < ns; i += kThreads, k++) {
-    if (!((pend >> k) & 1u)) continue;
-    const int cls = i >= nsGA;
-    const GridP& g = s.grid[cls];
-    if (s.misc[M_TREE + cls] != 1) continue;              // tree unavailable: keep the grid's answer
-    double2 sp = s.scene[i];
-    float qx, qy;
-    transform(Rt, sp.x, sp.y, qx, qy);
-    int32_t o = -1; float d = 0.0f;
-    int rc = kdreplay::nearest(rs.pts + g.first, rs.ind + g.first, rs.nodes + 2 * g.first + 4 * cls,
-                               s.misc[M_NNODE + cls], qx, qy, &o, &d);
-    if (rc != kdreplay::OK || o < 0) { atomicOr(&s.misc[M_TREEFAIL], 1); continue; }
-    // original index -> sorted slot: look inside the point's own cell
-    kdreplay::Pt p = rs.pts[g.first + o];
-    int ix = (int)__fmul_rn(__fsub_rn(p.x, g.minx), g.inv_h);
-    int iy = (int)__fmul_rn(__fsub_rn(p.y, g.miny), g.inv_h);
-    ix = min(max(ix, 0), g.G - 1); iy = min(max(iy, 0), g.G - 1);
-    const int cell = g.base + iy * g.G + ix;
-    for (int j = s.cstart[cell]; j < s.cstart[cell + 1]; j++)
-      if (s.morig[j] == (uint16_t)o) { s.slots[i] = (uint16_t)j; break; }
-    atomicAdd(&s.misc[M_REPLAYS], 1);
-  }
+  __syncthreads();
+  for (int w = tid; w <= (ns - 1) >> 5; w += kThreads) s.tiebits[w] = 0u;
   __syncthreads();
 }
 

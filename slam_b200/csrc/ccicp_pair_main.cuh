@@ -102,6 +102,8 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
       __syncthreads();
       if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; }
       for (int i = tid; i < ns; i += kThreads) s.slots[i] = (uint16_t)kNoSlot;   // no warm start for a new seed
+      for (int w = tid; w <= (ns - 1) >> 5 && ns > 0; w += kThreads) s.tiebits[w] = 0u;
+      __syncthreads();
 
       if (!model_ok) status |= CCICP_ST_TOO_FEW_MODEL;
       else if (!scene_ok) status |= CCICP_ST_TOO_FEW_SCENE;
@@ -111,9 +113,8 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
         for (int iter = 0; iter < a.max_iter; iter++) {
           double* red = s.red + (iter & 1) * (kWarps * 10);
           // ---- a4..a6: transform, nearest neighbour, gate; shifted sums of the accepted pairs
-          uint32_t pend = 0;
-          int k = 0;
-          for (int i = tid; i < ns; i += kThreads, k++) {          // loop A: search only (few live registers)
+          int pend = 0;
+          for (int i = tid; i < ns; i += kThreads) {          // loop A: search only (few live registers)
             const double2 sp = s.scene[i];
             float qx, qy;
             transform(Rt, sp.x, sp.y, qx, qy);
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
               nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, s.slots[i], best, bslot, tie);
               if (bslot >= 0 && (double)best < a.indist) {
                 slot = (unsigned)bslot;
-                if (tie && replay_on) pend |= 1u << (k & 31);
+                if (tie && replay_on) { pend = 1; atomicOr(&s.tiebits[i >> 5], 1u << (i & 31)); }
               }
             }
             s.slots[i] = (uint16_t)slot;
@@ -142,7 +143,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
 #pragma unroll
           for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&red[w * 10 + 8]; n += ip[0]; any_tie |= ip[1]; }
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
-            replay_ties(a, s, Rt, m0, nmGA, nmNGA, ns, nsGA, pend, tid);
+            replay_ties(a, s, Rt, ns, nsGA, tid);
             status |= CCICP_ST_TIE_REPLAY;
             sums_from_slots(s, Rt, ns, tid, pcx, pcy, v, cnt);
             const int wc = __reduce_add_sync(0xffffffffu, cnt);

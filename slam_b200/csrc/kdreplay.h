@@ -39,11 +39,19 @@ struct Node {
 enum { BUCKET = 12, STACK = 64 };
 enum { OK = 0, ERR_DEPTH = 1, ERR_NODES = 2, ERR_DEGENERATE = 3 };
 
-KD_HD float coord(const Pt* p, int i, int c) { return c == 0 ? p[i].x : p[i].y; }
+// Point access goes through an accessor `P` with `Pt operator()(int original_index) const`, and the index
+// permutation through any integer array type `I` (the device build keeps both in shared memory).
+struct PtrPts {
+  const Pt* p;
+  KD_HD Pt operator()(int i) const { return p[i]; }
+};
+template <class P>
+KD_HD float coord(const P& p, int i, int c) { Pt v = p(i); return c == 0 ? v.x : v.y; }
 
 // min/max of coordinate c over ind[l..u] (kdtree.cpp:235-269; min/max are
 // order independent so the pairwise walk is not reproduced).
-KD_HD void spread(const Pt* pts, const int32_t* ind, int c, int l, int u, float* lo, float* hi) {
+template <class P, class I>
+KD_HD void spread(const P& pts, const I* ind, int c, int l, int u, float* lo, float* hi) {
   float smin = coord(pts, ind[l], c), smax = smin;
   for (int i = l + 1; i <= u; i++) {
     float v = coord(pts, ind[i], c);
@@ -55,11 +63,12 @@ KD_HD void spread(const Pt* pts, const int32_t* ind, int c, int l, int u, float*
 
 // Builds the tree over n points.  ind[n] and nodes[max_nodes] are outputs;
 // returns OK or an ERR_* code; *n_nodes receives the node count; root is node 0.
-KD_FN int build(const Pt* pts, int n, int32_t* ind, Node* nodes, int max_nodes, int* n_nodes) {
+template <class P, class I>
+KD_FN int build(const P& pts, int n, I* ind, Node* nodes, int max_nodes, int* n_nodes) {
   struct Frame { int l, u, parent, node, m, stage; };
   Frame st[STACK];
   int sp = 0, nn = 0, ret = -1;
-  for (int i = 0; i < n; i++) ind[i] = i;
+  for (int i = 0; i < n; i++) ind[i] = (I)i;
   *n_nodes = 0;
   if (n <= 0) return OK;
   st[sp].l = 0; st[sp].u = n - 1; st[sp].parent = -1; st[sp].node = -1; st[sp].m = 0; st[sp].stage = 0; sp++;
@@ -105,7 +114,7 @@ KD_FN int build(const Pt* pts, int n, int32_t* ind, Node* nodes, int max_nodes, 
         if (coord(pts, ind[lb], c) <= average) {
           lb++;
         } else {
-          int32_t tmp = ind[lb]; ind[lb] = ind[ub]; ind[ub] = tmp;
+          I tmp = ind[lb]; ind[lb] = ind[ub]; ind[ub] = tmp;
           ub--;
         }
       }
@@ -173,7 +182,8 @@ KD_HD bool box_in_range(const Node& nd, float qx, float qy, float ballsize) {
 // Exact replay of n_nearest(q, 1): returns the ORIGINAL model index the
 // reference would report (or -1 when nothing lies within 1e38) and its float
 // squared distance.  Returns OK or ERR_DEPTH.
-KD_FN int nearest(const Pt* pts, const int32_t* ind, const Node* nodes, int n_nodes,
+template <class P, class I>
+KD_FN int nearest(const P& pts, const I* ind, const Node* nodes, int n_nodes,
                   float qx, float qy, int32_t* idx_out, float* dis_out) {
   struct Pending { int node; float extra; };
   Pending st[STACK];
@@ -200,12 +210,13 @@ KD_FN int nearest(const Pt* pts, const int32_t* ind, const Node* nodes, int n_no
     if (cur >= 0) {                                               // leaf scan (:604-681, nn == 1, rearranged data)
       const Node& nd = nodes[cur];
       for (int i = nd.l; i <= nd.u; i++) {
-        int o = ind[i];
-        float dx = pts[o].x - qx;
+        int o = (int)ind[i];
+        const Pt po = pts(o);
+        float dx = po.x - qx;
         float dis = 0.0f;
         dis += dx * dx;
         if (dis > ballsize) continue;
-        float dy = pts[o].y - qy;
+        float dy = po.y - qy;
         dis += dy * dy;
         if (dis > ballsize) continue;
         have = true; best = o; bestd = dis; ballsize = dis;       // push (first) or replace (later, dis <= best)
@@ -217,6 +228,168 @@ KD_FN int nearest(const Pt* pts, const int32_t* ind, const Node* nodes, int n_no
       int far_ = st[sp].node;
       float extra = st[sp].extra;
       if (far_ >= 0 && extra * extra < ballsize && box_in_range(nodes[far_], qx, qy, ballsize)) {
+        cur = far_; found = true; break;
+      }
+    }
+    if (!found) break;
+  }
+  if (have) { *idx_out = best; *dis_out = bestd; }
+  return OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Lazy variant used by the kernel: the tree is materialised only along the paths the tied queries actually
+// traverse.  A node is split the first time a search reaches it; the split reproduces exactly what the eager
+// build would have produced for that node because (a) the partition of a node depends only on the order its
+// ancestors' partitions left in ind[l..u], (b) the "approximate box" a node inherits (kdtree.cpp:153-168) is
+// carried down explicitly in abox, and (c) every bounding box the search consults (cut_val_left/right,
+// box_in_search_range) is the TRUE box of a range, which is computed directly from the points of that range.
+struct LNode {
+  float tbox[4];             // true bounding box of ind[l..u]: {x.lo, x.hi, y.lo, y.hi}
+  float abox[4];             // the box the eager build would hold for this node while choosing its cut dimension
+  float cut_val, cut_val_left, cut_val_right;
+  int32_t cut_dim;           // -1 terminal, -2 internal but not split yet, 0/1 split on that coordinate
+  int32_t l, u, left, right;
+};
+enum { LEAF = -1, UNSPLIT = -2 };
+
+template <class P, class I>
+KD_FN int lazy_init(const P& pts, int n, I* ind, LNode* nodes, int* n_nodes) {
+  for (int i = 0; i < n; i++) ind[i] = (I)i;
+  *n_nodes = 0;
+  if (n <= 0) return OK;
+  LNode r;
+  r.l = 0; r.u = n - 1; r.left = r.right = -1;
+  r.cut_val = r.cut_val_left = r.cut_val_right = 0.0f;
+  spread(pts, ind, 0, 0, n - 1, &r.tbox[0], &r.tbox[1]);
+  spread(pts, ind, 1, 0, n - 1, &r.tbox[2], &r.tbox[3]);
+  for (int i = 0; i < 4; i++) r.abox[i] = r.tbox[i];
+  r.cut_dim = (n - 1 <= BUCKET) ? LEAF : UNSPLIT;
+  nodes[0] = r;
+  *n_nodes = 1;
+  return OK;
+}
+
+template <class P, class I>
+KD_FN int lazy_split(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n_nodes, int id) {
+  LNode nd = nodes[id];
+  const int l = nd.l, u = nd.u;
+  int c = -1;
+  float maxspread = 0.0f;
+  for (int i = 0; i < 2; i++) {
+    float sprd = nd.abox[2 * i + 1] - nd.abox[2 * i];
+    if (sprd > maxspread) { maxspread = sprd; c = i; }
+  }
+  if (c < 0) return ERR_DEGENERATE;
+  float sum = 0.0f;
+  for (int k = l; k <= u; k++) sum += coord(pts, ind[k], c);
+  const float average = sum / (float)(u - l + 1);
+  int lb = l, ub = u;
+  while (lb < ub) {
+    if (coord(pts, ind[lb], c) <= average) {
+      lb++;
+    } else {
+      I tmp = ind[lb]; ind[lb] = ind[ub]; ind[ub] = tmp;
+      ub--;
+    }
+  }
+  const int m = (coord(pts, ind[lb], c) <= average) ? lb : lb - 1;
+  int child[2] = {-1, -1};
+  for (int sde = 0; sde < 2; sde++) {
+    const int cl = sde ? m + 1 : l, cu = sde ? u : m;
+    if (cu < cl) continue;
+    if (cl == l && cu == u) return ERR_DEGENERATE;       // the reference would recurse forever here
+    if (*n_nodes >= max_nodes) return ERR_NODES;
+    LNode ch;
+    ch.l = cl; ch.u = cu; ch.left = ch.right = -1;
+    ch.cut_val = ch.cut_val_left = ch.cut_val_right = 0.0f;
+    spread(pts, ind, 0, cl, cu, &ch.tbox[0], &ch.tbox[1]);
+    spread(pts, ind, 1, cl, cu, &ch.tbox[2], &ch.tbox[3]);
+    for (int i = 0; i < 4; i++) ch.abox[i] = nd.abox[i];
+    ch.abox[2 * c] = ch.tbox[2 * c]; ch.abox[2 * c + 1] = ch.tbox[2 * c + 1];
+    ch.cut_dim = (cu - cl <= BUCKET) ? LEAF : UNSPLIT;
+    child[sde] = *n_nodes;
+    nodes[(*n_nodes)++] = ch;
+  }
+  nd.left = child[0]; nd.right = child[1];
+  if (nd.right < 0) {
+    nd.cut_val = nodes[nd.left].tbox[2 * c + 1];
+    nd.cut_val_left = nd.cut_val_right = nd.cut_val;
+  } else if (nd.left < 0) {
+    nd.cut_val = nodes[nd.right].tbox[2 * c + 1];
+    nd.cut_val_left = nd.cut_val_right = nd.cut_val;
+  } else {
+    nd.cut_val_right = nodes[nd.right].tbox[2 * c];
+    nd.cut_val_left = nodes[nd.left].tbox[2 * c + 1];
+    nd.cut_val = (float)((double)(nd.cut_val_left + nd.cut_val_right) / 2.0);
+  }
+  nd.cut_dim = c;
+  nodes[id] = nd;
+  return OK;
+}
+
+KD_HD bool lbox_in_range(const LNode& nd, float qx, float qy, float ballsize) {
+  float d0 = dis_from_bnd(qx, nd.tbox[0], nd.tbox[1]);
+  float dis2 = 0.0f;
+  dis2 += d0 * d0;
+  if (dis2 > ballsize) return false;
+  float d1 = dis_from_bnd(qy, nd.tbox[2], nd.tbox[3]);
+  dis2 += d1 * d1;
+  if (dis2 > ballsize) return false;
+  return true;
+}
+
+// Exact replay of n_nearest(q, 1) on the lazily materialised tree (same traversal as nearest()).
+template <class P, class I>
+KD_FN int lazy_nearest(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n_nodes,
+                       float qx, float qy, int32_t* idx_out, float* dis_out) {
+  struct Pending { int node; float extra; };
+  Pending st[STACK];
+  int sp = 0;
+  float ballsize = 1.0e38f;
+  bool have = false;
+  int32_t best = -1;
+  float bestd = 0.0f;
+  *idx_out = -1; *dis_out = 0.0f;
+  if (*n_nodes <= 0) return OK;
+  int cur = 0;
+  for (;;) {
+    while (cur >= 0 && nodes[cur].cut_dim != LEAF) {
+      if (nodes[cur].cut_dim == UNSPLIT) {
+        int rc = lazy_split(pts, ind, nodes, max_nodes, n_nodes, cur);
+        if (rc != OK) return rc;
+      }
+      const LNode& nd = nodes[cur];
+      float qval = nd.cut_dim == 0 ? qx : qy;
+      int closer, farther;
+      float extra;
+      if (qval < nd.cut_val) { closer = nd.left; farther = nd.right; extra = nd.cut_val_right - qval; }
+      else { closer = nd.right; farther = nd.left; extra = qval - nd.cut_val_left; }
+      if (sp >= STACK) return ERR_DEPTH;
+      st[sp].node = farther; st[sp].extra = extra; sp++;
+      cur = closer;
+    }
+    if (cur >= 0) {
+      const int l = nodes[cur].l, u = nodes[cur].u;
+      for (int i = l; i <= u; i++) {
+        int o = (int)ind[i];
+        const Pt po = pts(o);
+        float dx = po.x - qx;
+        float dis = 0.0f;
+        dis += dx * dx;
+        if (dis > ballsize) continue;
+        float dy = po.y - qy;
+        dis += dy * dy;
+        if (dis > ballsize) continue;
+        have = true; best = o; bestd = dis; ballsize = dis;
+      }
+    }
+    bool found = false;
+    while (sp > 0) {
+      sp--;
+      int far_ = st[sp].node;
+      float extra = st[sp].extra;
+      if (far_ >= 0 && extra * extra < ballsize && lbox_in_range(nodes[far_], qx, qy, ballsize)) {
         cur = far_; found = true; break;
       }
     }

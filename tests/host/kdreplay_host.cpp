@@ -14,7 +14,7 @@ int kdr_tree(const double* pts, int n, int32_t* ind_out, float* nodes_out, int m
   for (int i = 0; i < n; i++) { p[i].x = (float)pts[2 * i]; p[i].y = (float)pts[2 * i + 1]; }
   std::vector<kdreplay::Node> nodes(2 * (n > 0 ? n : 1) + 2);
   int nn = 0;
-  int rc = kdreplay::build(p.data(), n, ind_out, nodes.data(), (int)nodes.size(), &nn);
+  int rc = kdreplay::build(kdreplay::PtrPts{p.data()}, n, ind_out, nodes.data(), (int)nodes.size(), &nn);
   if (rc != kdreplay::OK) return -1000 - rc;
   if (nn > max_nodes) return -nn;
   for (int k = 0; k < nn; k++) {
@@ -37,12 +37,31 @@ int kdr_nn(const double* pts, int n, const float* q, int nq, int32_t* idx, float
   std::vector<kdreplay::Node> nodes(2 * (n > 0 ? n : 1) + 2);
   std::vector<int32_t> ind(n > 0 ? n : 1);
   int nn = 0;
-  int rc = kdreplay::build(p.data(), n, ind.data(), nodes.data(), (int)nodes.size(), &nn);
+  int rc = kdreplay::build(kdreplay::PtrPts{p.data()}, n, ind.data(), nodes.data(), (int)nodes.size(), &nn);
   if (rc != kdreplay::OK) return -1000 - rc;
   for (int i = 0; i < nq; i++) {
-    rc = kdreplay::nearest(p.data(), ind.data(), nodes.data(), nn, q[2 * i], q[2 * i + 1], &idx[i], &dis[i]);
+    rc = kdreplay::nearest(kdreplay::PtrPts{p.data()}, ind.data(), nodes.data(), nn, q[2 * i], q[2 * i + 1], &idx[i], &dis[i]);
     if (rc != kdreplay::OK) return -2000 - rc;
   }
+  return 0;
+}
+
+
+// Lazy tree (what the kernel uses): answers must equal the reference's for any query order.
+int kdr_nn_lazy(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis, int* nodes_built) {
+  std::vector<kdreplay::Pt> p(n > 0 ? n : 1);
+  for (int i = 0; i < n; i++) { p[i].x = (float)pts[2 * i]; p[i].y = (float)pts[2 * i + 1]; }
+  std::vector<kdreplay::LNode> nodes(2 * (n > 0 ? n : 1) + 8);
+  std::vector<uint16_t> ind(n > 0 ? n : 1);
+  int nn = 0;
+  kdreplay::PtrPts acc{p.data()};
+  int rc = kdreplay::lazy_init(acc, n, ind.data(), nodes.data(), &nn);
+  if (rc != kdreplay::OK) return -1000 - rc;
+  for (int i = 0; i < nq; i++) {
+    rc = kdreplay::lazy_nearest(acc, ind.data(), nodes.data(), (int)nodes.size(), &nn, q[2 * i], q[2 * i + 1], &idx[i], &dis[i]);
+    if (rc != kdreplay::OK) return -2000 - rc;
+  }
+  if (nodes_built) *nodes_built = nn;
   return 0;
 }
 
