@@ -159,7 +159,7 @@ def load_traffic():
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from slam_b200 import capi, scangen
+    from slam_b200 import capi, scangen, sharding
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
@@ -169,7 +169,9 @@ def gpu_arm(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
 
     n_pairs = args.pairs
-    batch = scangen.generate(SEED0 + rank * n_pairs, n_pairs, config=1, pinned=capi.pinned_array)
+    seed_lo, n_local = sharding.shard_seeds(SEED0, n_pairs * world, rank, world)     # contiguous pair ranges
+    assert n_local == n_pairs
+    batch = scangen.generate(seed_lo, n_pairs, config=1, pinned=capi.pinned_array)
     init_h = capi.pinned_array((n_pairs, 6), np.float64)
     init_h[:] = batch.init_Rt()
     out_h = capi.pinned_array((n_pairs,), capi.RESULT_DTYPE)
@@ -183,7 +185,6 @@ def gpu_arm(args, rank, world, local_rank):
     d_moff, d_soff = t(batch.model_off, np.int32), t(batch.scene_off, np.int32)
     d_init = t(init_h, np.float64)
     d_out = torch.zeros(n_pairs * capi.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
-    gathered = torch.zeros(world * d_out.numel(), dtype=torch.uint8, device=dev) if world > 1 else None
     stream = torch.cuda.Stream(device=dev)
 
     def step_device():
@@ -191,7 +192,8 @@ def gpu_arm(args, rank, world, local_rank):
                                   d_init.data_ptr(), prm, d_out.data_ptr(), 0, batch.max_model, batch.max_scene,
                                   stream.cuda_stream)
         if world > 1:      # the path's only exchange: gather the per-pair records
-            dist.all_gather_into_tensor(gathered, d_out)
+            return sharding.gather_records(d_out, world, n_pairs * world)
+        return d_out
 
     def barrier():
         if world > 1:

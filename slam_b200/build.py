@@ -91,6 +91,19 @@ def build_host_tests(force=False, verbose=False):
     return out
 
 
+def build_callsite(force=False, verbose=False):
+    """The reference call site compiled against the drop-in headers/library (tests/host/callsite_b200)."""
+    d = os.path.join(ROOT, "tests", "host")
+    out = os.path.join(d, "callsite_b200")
+    src = os.path.join(d, "callsite_demo.cpp")
+    if not os.path.exists(os.path.join(LIB, "libccicp2d.so")):
+        return None
+    if force or _newer(out, [src, os.path.join(LIB, "libccicp2d.so")]):
+        _run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-o", out, src, "-L" + LIB,
+              "-lccicp2d", "-lccicp2d_b200", "-Wl,-rpath,$ORIGIN/../../slam_b200/lib"], verbose)
+    return out
+
+
 def build_oracle(force=False, verbose=False):
     """Builds the checker (TEST INFRASTRUCTURE); building it is not using it."""
     od = os.path.join(ROOT, "oracle")
@@ -105,6 +118,7 @@ def build_all(force=False, verbose=False):
     build_scangen(force, verbose)
     build_facade(force, verbose)
     build_host_tests(force, verbose)
+    build_callsite(force, verbose)
     build_oracle(force, verbose)
 
 

@@ -1,0 +1,63 @@
+"""CPU check of the product's tie-replay code (slam_b200/csrc/kdreplay.h compiled for the host): the eager build
+must reproduce the reference kd-tree node for node, and both the eager and the lazy traversal must return the
+reference's n_nearest(q,1) answer, including on tie-heavy lattice clouds."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "host", "libkdreplay_host.so")
+P = C.c_void_p
+
+
+@pytest.fixture(scope="module")
+def kd():
+    if not os.path.exists(LIB):
+        pytest.fail("tests/host/libkdreplay_host.so missing: run __graft_entry__.build()")
+    return C.CDLL(LIB)
+
+
+def clouds():
+    rng = np.random.default_rng(0)
+    for trial in range(24):
+        n = int(rng.integers(5, 2500))
+        kind = trial % 4
+        if kind == 0:
+            pts = rng.uniform(-10, 10, (n, 2))
+        elif kind == 1:
+            pts = np.round(rng.uniform(-40, 40, (n, 2)))          # lattice: duplicates and ties
+        elif kind == 2:
+            a = np.sort(rng.uniform(-2, 2, n)); r = 5 + 0.01 * rng.standard_normal(n)
+            pts = np.stack([r * np.cos(a), r * np.sin(a)], 1)      # a scan-like arc
+        else:
+            pts = np.round(rng.uniform(-20, 20, (n, 2)) * 2) / 2
+        nq = [3, 40, 2500][trial % 3]
+        q = np.round(rng.uniform(-42, 42, (nq, 2)) * 2) / 2 if kind in (1, 3) else rng.uniform(-12, 12, (nq, 2))
+        yield np.ascontiguousarray(pts, np.float64), np.ascontiguousarray(q, np.float32)
+
+
+def test_eager_tree_matches_reference(kd, oracle):
+    for pts, _ in clouds():
+        n = len(pts)
+        ind = np.zeros(n, np.int32); nodes = np.zeros(10 * (2 * n + 2), np.float32)
+        nn = kd.kdr_tree(pts.ctypes.data_as(P), n, ind.ctypes.data_as(P), nodes.ctypes.data_as(P), 2 * n + 2)
+        rn, rind, rnodes = oracle.tree(pts)
+        assert nn == rn and (ind == rind).all()
+        assert (nodes[:10 * nn].reshape(-1, 10) == rnodes).all()     # == : -0.0 equals +0.0
+
+
+def test_eager_and_lazy_search_match_reference(kd, oracle):
+    for pts, q in clouds():
+        n, nq = len(pts), len(q)
+        ridx, rdis = oracle.nn(pts, q)
+        idx = np.zeros(nq, np.int32); dis = np.zeros(nq, np.float32)
+        assert kd.kdr_nn(pts.ctypes.data_as(P), n, q.ctypes.data_as(P), nq, idx.ctypes.data_as(P), dis.ctypes.data_as(P)) == 0
+        assert (idx == ridx).all() and (dis == rdis).all()
+        built = C.c_int(0)
+        idx[:] = -7
+        assert kd.kdr_nn_lazy(pts.ctypes.data_as(P), n, q.ctypes.data_as(P), nq, idx.ctypes.data_as(P),
+                              dis.ctypes.data_as(P), C.byref(built)) == 0
+        assert (idx == ridx).all() and (dis == rdis).all()
+        assert built.value <= oracle.tree(pts)[0]        # the lazy tree never holds more nodes than the full one

@@ -1,0 +1,62 @@
+"""Host-side multi-rank logic on CPU: world_size-2 and -3 gloo process groups exercise the pair sharding and the
+record gather that bench.py runs over NCCL."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from slam_b200 import capi, sharding
+
+
+def test_shard_range_is_a_partition():
+    for n in (0, 1, 7, 4096, 262144, 1000003):
+        for world in (1, 2, 3, 4, 8):
+            edges = [sharding.shard_range(n, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == n
+            assert all(edges[r][1] == edges[r + 1][0] for r in range(world - 1))
+            sizes = [hi - lo for lo, hi in edges]
+            assert max(sizes) - min(sizes) <= 1
+    assert sharding.shard_seeds(10**6, 262144, 3, 8) == (10**6 + 3 * 32768, 32768)
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, n_total, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = sharding.shard_range(n_total, rank, world)
+    rec = np.zeros(hi - lo, capi.RESULT_DTYPE)
+    rec["num_corr"] = np.arange(lo, hi)            # stands in for "the record of pair p"
+    rec["t"][:, 0] = np.arange(lo, hi) * 0.5
+    rec["best_seed"] = rank
+    local = torch.from_numpy(rec.view(np.uint8).copy())
+    out = sharding.records_view(sharding.gather_records(local, world, n_total))
+    ok = (len(out) == n_total and (out["num_corr"] == np.arange(n_total)).all()
+          and (out["t"][:, 0] == np.arange(n_total) * 0.5).all())
+    tm = torch.tensor([float(rank + 1)])
+    dist.all_reduce(tm, op=dist.ReduceOp.MAX)        # bench.py's max-over-ranks timing reduction
+    q.put((rank, bool(ok), float(tm.item())))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_total", [(2, 64), (2, 33), (3, 100)])
+def test_gather_records_gloo(world, n_total):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_total, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(r[0] for r in res) == list(range(world))
+    assert all(r[1] for r in res) and all(r[2] == float(world) for r in res)
