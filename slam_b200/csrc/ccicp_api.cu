@@ -21,6 +21,8 @@ struct ccicp_ctx {
   int sm_count = 0;
   int max_smem_optin = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr, kstream[2] = {nullptr, nullptr};   // chunked host path: H2D overlaps compute
+  cudaEvent_t chunk_ev[16] = {};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
   bool timed = false, timed_copies = false;
   void* timed_stream = nullptr;
@@ -69,11 +71,11 @@ int max_cells_for(int max_model) {
   return best;
 }
 
-int launch_icp(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy, const int32_t* d_model_off,
+int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy, const int32_t* d_model_off,
                const double* d_scene_xy, const int32_t* d_scene_off, const double* d_init_Rt,
                const ccicp_params* prm, ccicp_result* d_out, int32_t* d_corr, int32_t max_model, int32_t max_scene,
                int32_t max_cells, int64_t total_scene, cudaStream_t st) {
-  ctx->info.n_launches = 0;
+  if (slot == 0) ctx->info.n_launches = 0;
   if (n_pairs == 0) return CCICP_OK;
   if (max_model > CCICP_MAX_POINTS - 1 || max_scene > CCICP_MAX_POINTS) return CCICP_E_TOO_LARGE;
   IcpArgs a{};
@@ -107,31 +109,39 @@ int launch_icp(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* d
     if (rc) return rc;
     kernel_out = (ccicp_result*)ctx->all_results.p;
   }
+  // `slot` separates launches that may be in flight together (chunked host path): own work counter, own scratch
   int rc = reserve(ctx, ctx->counter, 256);
   if (rc) return rc;
   const size_t per_cta = replay_scratch_bytes(max_model);
-  rc = reserve(ctx, ctx->scratch, per_cta * (size_t)grid);
-  if (rc) return rc;
+  const size_t per_slot = per_cta * (size_t)resident;
+  if (slot == 0 || ctx->scratch.cap < per_slot * 2) {
+    if (ctx->scratch.cap < per_slot * 2) {
+      if (slot != 0) return CCICP_E_INVALID;      // sized by the first launch of a call
+      rc = reserve(ctx, ctx->scratch, per_slot * 2);
+      if (rc) return rc;
+    }
+  }
 
   a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
   a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
-  a.work_counter = (int32_t*)ctx->counter.p;
-  a.scratch = (char*)ctx->scratch.p; a.scratch_per_cta = per_cta;
+  a.work_counter = (int32_t*)ctx->counter.p + (slot & 15);
+  a.scratch = (char*)ctx->scratch.p + (size_t)(slot & 1) * per_slot; a.scratch_per_cta = per_cta;
+  a.pair_base = pair_base;
   a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
   a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
   a.total_scene = total_scene; a.max_model = max_model;
 
-  CK(cudaMemsetAsync(ctx->counter.p, 0, 4, st));
-  CK(cudaEventRecord(ctx->ev[2], st));
+  CK(cudaMemsetAsync(a.work_counter, 0, 4, st));
+  if (slot == 0) CK(cudaEventRecord(ctx->ev[2], st));
   icp_pair_kernel<<<grid, kThreads, smem, st>>>(a);
   CK(cudaGetLastError());
-  ctx->info.n_launches = 1;
+  ctx->info.n_launches += 1;
   if (best_of) {
     const int threads = 128, warps_per_block = threads / 32;
     select_best_seed_kernel<<<(n_pairs + warps_per_block - 1) / warps_per_block, threads, 0, st>>>(
         kernel_out, d_out, d_scene_off, n_pairs, n_seeds, prm->min_corr_frac);
     CK(cudaGetLastError());
-    ctx->info.n_launches = 2;
+    ctx->info.n_launches += 1;
   }
   CK(cudaEventRecord(ctx->ev[3], st));
   ctx->timed = true; ctx->timed_stream = (void*)st;
@@ -200,6 +210,10 @@ int ccicp_create(ccicp_ctx** out, int device) {
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
   for (auto& ev : ctx->ev)
     if (cudaEventCreate(&ev) != cudaSuccess) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
+  bool ok = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+  for (auto& ks : ctx->kstream) ok = ok && cudaStreamCreateWithFlags(&ks, cudaStreamNonBlocking) == cudaSuccess;
+  for (auto& ev : ctx->chunk_ev) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
   *out = ctx;
   return CCICP_OK;
 }
@@ -212,6 +226,9 @@ int ccicp_destroy(ccicp_ctx* ctx) {
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+  for (auto& ev : ctx->chunk_ev) if (ev) cudaEventDestroy(ev);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  for (auto& ks : ctx->kstream) if (ks) cudaStreamDestroy(ks);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return CCICP_OK;
@@ -234,7 +251,7 @@ int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds
     total_scene = last;
   }
   ctx->timed_copies = false;
-  return launch_icp(ctx, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt, params, d_out,
+  return launch_icp(ctx, 0, 0, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt, params, d_out,
                     d_corr_idx, max_model, max_scene, 0, total_scene, st);
 }
 
@@ -280,23 +297,48 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   if ((rc = reserve(ctx, ctx->d_out, n_out * sizeof(ccicp_result)))) return rc;
   if (corr_idx && (rc = reserve(ctx, ctx->d_corr, (size_t)n_scene * n_seeds * 4 + 16))) return rc;
 
-  CK(cudaEventRecord(ctx->ev[0], st));
-  if (n_model) CK(cudaMemcpyAsync(ctx->d_model.p, model_xy, (size_t)n_model * 16, cudaMemcpyHostToDevice, st));
-  if (n_scene) CK(cudaMemcpyAsync(ctx->d_scene.p, scene_xy, (size_t)n_scene * 16, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(ctx->d_moff.p, model_off, off_bytes, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(ctx->d_soff.p, scene_off, off_bytes, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(ctx->d_init.p, init_Rt, n_prob * 48, cudaMemcpyHostToDevice, st));
-  CK(cudaEventRecord(ctx->ev[1], st));
-  rc = launch_icp(ctx, n_pairs, n_seeds, (const double*)ctx->d_model.p, (const int32_t*)ctx->d_moff.p,
-                  (const double*)ctx->d_scene.p, (const int32_t*)ctx->d_soff.p, (const double*)ctx->d_init.p, params,
-                  (ccicp_result*)ctx->d_out.p, corr_idx ? (int32_t*)ctx->d_corr.p : nullptr, max_model, max_scene,
-                  max_cells, n_scene, st);
-  if (rc) return rc;
-  CK(cudaEventRecord(ctx->ev[4], st));
-  CK(cudaMemcpyAsync(out, ctx->d_out.p, n_out * sizeof(ccicp_result), cudaMemcpyDeviceToHost, st));
-  if (corr_idx && n_scene) CK(cudaMemcpyAsync(corr_idx, ctx->d_corr.p, (size_t)n_scene * n_seeds * 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaEventRecord(ctx->ev[5], st));
-  CK(cudaStreamSynchronize(st));
+  // Chunked pipeline: the H2D copy of chunk c+1 (copy stream) overlaps the kernel of chunk c; consecutive
+  // chunks run on two compute streams so the tail of one kernel overlaps the head of the next.  The offsets
+  // are absolute, so every chunk's kernel indexes the same device arrays with a different pair_base.
+  int n_chunks = 1;
+  if (n_seeds == 1 && !corr_idx) {
+    n_chunks = n_pairs / 1024;
+    if (n_chunks > 8) n_chunks = 8;
+    if (n_chunks < 1) n_chunks = 1;
+  }
+  cudaStream_t cs = ctx->copy_stream;
+  CK(cudaEventRecord(ctx->ev[0], cs));
+  CK(cudaMemcpyAsync(ctx->d_moff.p, model_off, off_bytes, cudaMemcpyHostToDevice, cs));
+  CK(cudaMemcpyAsync(ctx->d_soff.p, scene_off, off_bytes, cudaMemcpyHostToDevice, cs));
+  for (int c = 0; c < n_chunks; c++) {
+    const int32_t p0 = (int32_t)((int64_t)n_pairs * c / n_chunks), p1 = (int32_t)((int64_t)n_pairs * (c + 1) / n_chunks);
+    const int64_t m0 = model_off[2 * (size_t)p0], m1 = model_off[2 * (size_t)p1];
+    const int64_t s0 = scene_off[2 * (size_t)p0], s1 = scene_off[2 * (size_t)p1];
+    if (m1 > m0) CK(cudaMemcpyAsync((char*)ctx->d_model.p + m0 * 16, model_xy + 2 * m0, (size_t)(m1 - m0) * 16, cudaMemcpyHostToDevice, cs));
+    if (s1 > s0) CK(cudaMemcpyAsync((char*)ctx->d_scene.p + s0 * 16, scene_xy + 2 * s0, (size_t)(s1 - s0) * 16, cudaMemcpyHostToDevice, cs));
+    CK(cudaMemcpyAsync((char*)ctx->d_init.p + (size_t)p0 * n_seeds * 48, init_Rt + (size_t)p0 * n_seeds * 6,
+                       (size_t)(p1 - p0) * n_seeds * 48, cudaMemcpyHostToDevice, cs));
+    CK(cudaEventRecord(ctx->chunk_ev[c], cs));
+    if (c == n_chunks - 1) CK(cudaEventRecord(ctx->ev[1], cs));
+    cudaStream_t ks = n_chunks == 1 ? st : ctx->kstream[c & 1];
+    CK(cudaStreamWaitEvent(ks, ctx->chunk_ev[c], 0));
+    rc = launch_icp(ctx, p0, c, p1 - p0, n_seeds, (const double*)ctx->d_model.p, (const int32_t*)ctx->d_moff.p,
+                    (const double*)ctx->d_scene.p, (const int32_t*)ctx->d_soff.p, (const double*)ctx->d_init.p, params,
+                    (ccicp_result*)ctx->d_out.p, corr_idx ? (int32_t*)ctx->d_corr.p : nullptr, max_model, max_scene,
+                    max_cells, n_scene, ks);
+    if (rc) { cudaDeviceSynchronize(); return rc; }
+    if (c == n_chunks - 1) CK(cudaEventRecord(ctx->ev[4], ks));
+    const size_t o0 = best_of ? (size_t)p0 : (size_t)p0 * n_seeds, o1 = best_of ? (size_t)p1 : (size_t)p1 * n_seeds;
+    CK(cudaMemcpyAsync(out + o0, (char*)ctx->d_out.p + o0 * sizeof(ccicp_result), (o1 - o0) * sizeof(ccicp_result),
+                       cudaMemcpyDeviceToHost, ks));
+    if (c == n_chunks - 1) {
+      if (corr_idx && n_scene) CK(cudaMemcpyAsync(corr_idx, ctx->d_corr.p, (size_t)n_scene * n_seeds * 4, cudaMemcpyDeviceToHost, ks));
+      CK(cudaEventRecord(ctx->ev[5], ks));
+    }
+  }
+  CK(cudaStreamSynchronize(cs));
+  if (n_chunks == 1) CK(cudaStreamSynchronize(st));
+  else { CK(cudaStreamSynchronize(ctx->kstream[0])); CK(cudaStreamSynchronize(ctx->kstream[1])); }
   ctx->timed_copies = true;
   return CCICP_OK;
 }

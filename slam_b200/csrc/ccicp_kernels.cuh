@@ -47,6 +47,7 @@ struct IcpArgs {
   int32_t* work_counter;
   char* scratch; size_t scratch_per_cta;   // tie-replay trees
   int32_t n_pairs, n_seeds, seeds_per_item, items_per_pair;
+  int32_t pair_base;             // this launch registers pairs [pair_base, pair_base + n_pairs)
   int32_t max_iter; uint32_t flags;
   double min_delta, indist;
   int64_t total_scene;           // corr_idx seed stride (scene points in the whole batch)

@@ -74,8 +74,8 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
     __syncthreads();
     const int item = s.misc[M_WORK];
     if (item >= n_items) break;
-    const int pair = item / a.items_per_pair;
-    const int seed0 = (item - pair * a.items_per_pair) * a.seeds_per_item;
+    const int pair = a.pair_base + item / a.items_per_pair;
+    const int seed0 = (item % a.items_per_pair) * a.seeds_per_item;
     const int seed1 = min(seed0 + a.seeds_per_item, a.n_seeds);
 
     const int m0 = a.model_off[2 * pair], nmGA = a.model_off[2 * pair + 1] - m0, nmNGA = a.model_off[2 * pair + 2] - a.model_off[2 * pair + 1];
