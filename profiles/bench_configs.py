@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""Timing of the BASELINE.json configs that are not the bench.py line (C3 sample, C4, C5) on one GPU.
+Reports the ICP kernel's own device time (CUDA events inside the library) and the host-call wall time.
+usage: python profiles/bench_configs.py [c3] [c4] [c5] [--pairs N]"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from slam_b200 import capi, scangen  # noqa: E402
+
+
+def run(ctx, name, b, prm, n_seeds=1, init=None, reps=3):
+    init = b.init_Rt() if init is None else init
+    out = None
+    k_ms, w_ms = [], []
+    for _ in range(reps + 1):
+        t0 = time.perf_counter()
+        out = ctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, init, prm, n_seeds=n_seeds)
+        w_ms.append((time.perf_counter() - t0) * 1e3)
+        k_ms.append(ctx.launch_info().last_kernel_ms)
+    li = ctx.launch_info()
+    k, w = float(np.min(k_ms[1:])), float(np.min(w_ms[1:]))
+    n_prob = b.n_pairs * n_seeds
+    print(json.dumps({"config": name, "pairs": b.n_pairs, "seeds": n_seeds, "kernel_ms": k, "host_call_ms": w,
+                      "problems_per_s_kernel": n_prob / (k * 1e-3), "problems_per_s_host_call": n_prob / (w * 1e-3),
+                      "variant": "l2" if li.kernel_variant else "on-chip", "grid": li.grid, "block": li.block,
+                      "regs": li.regs_per_thread, "smem": li.smem_bytes, "n_launches": li.n_launches,
+                      "mean_num_corr": float(out["num_corr"].mean()), "mean_iters": float(out["iters"].mean()),
+                      "tie_replay_pairs": int((out["status"] & capi.ST_TIE_REPLAY != 0).sum())}), flush=True)
+    return out
+
+
+def main():
+    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["c3", "c4", "c5"]
+    pairs = int(sys.argv[sys.argv.index("--pairs") + 1]) if "--pairs" in sys.argv else 0
+    ctx = capi.Context(0)
+    prm = capi.fixed_iter_params(30)
+    if "c2" in which:
+        run(ctx, "C2 odometry 1081-beam", scangen.generate(1000, pairs or 4096, config=1), prm)
+    if "c3" in which:
+        run(ctx, "C3 loop-closure 1081-beam", scangen.generate(10**6, pairs or 16384, config=3), prm)
+    if "c4" in which:
+        run(ctx, "C4 dense 32768-point", scangen.generate(5000, pairs or 148, config=4), prm, reps=2)
+    if "c5" in which:
+        P, S = pairs or 256, 256
+        b = scangen.generate(2000, P, config=1)
+        init = np.concatenate([scangen.pose_to_Rt(scangen.hypotheses(int(s), S)) for s in b.seeds], 0)
+        prm5 = capi.fixed_iter_params(30, flags=capi.F_BEST_OF_SEEDS)
+        run(ctx, "C5 256 seeds best-of", b, prm5, n_seeds=S, init=init, reps=2)
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -25,8 +25,9 @@ struct ccicp_ctx {
   cudaEvent_t chunk_ev[16] = {};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
   bool timed = false, timed_copies = false;
+  bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the L2 variant
   void* timed_stream = nullptr;
-  DevBuf counter, scratch, all_results;
+  DevBuf counter, scratch, all_results, workspace;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
   ccicp_launch_info info{};
   std::string last_err;
@@ -83,11 +84,20 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   a.scap = round_up(max_scene < 32 ? 32 : max_scene, 32);
   a.ccap = max_cells > 0 ? max_cells : max_cells_for(max_model);
   if (a.ccap < 64) a.ccap = 64;
-  const size_t smem = smem_bytes(a.mcap, a.scap, a.ccap);
-  if (smem > (size_t)ctx->max_smem_optin) return CCICP_E_TOO_LARGE;
-  CK(cudaFuncSetAttribute(icp_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // on-chip variant when the pair's working set fits the SM's shared memory, else the L2 variant
+  cudaFuncAttributes fa_on;
+  CK(cudaFuncGetAttributes(&fa_on, icp_pair_kernel));
+  size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false);
+  const bool use_l2 = smem + fa_on.sharedSizeBytes > (size_t)ctx->max_smem_optin || ctx->force_l2;
+  const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
   int occ = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_kernel, kThreads, smem));
+  if (use_l2) {
+    smem = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_l2_kernel, threads, 0));
+  } else {
+    CK(cudaFuncSetAttribute(icp_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_kernel, threads, smem));
+  }
   if (occ < 1) return CCICP_E_TOO_LARGE;
   const int resident = occ * ctx->sm_count;
 
@@ -122,6 +132,16 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     }
   }
 
+  if (use_l2) {
+    a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true);
+    const size_t ws_slot = a.workspace_per_cta * (size_t)resident;
+    if (ctx->workspace.cap < ws_slot * 2) {
+      if (slot != 0) return CCICP_E_INVALID;
+      rc = reserve(ctx, ctx->workspace, ws_slot * 2);
+      if (rc) return rc;
+    }
+    a.workspace = (char*)ctx->workspace.p + (size_t)(slot & 1) * ws_slot;
+  }
   a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
   a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
   a.work_counter = (int32_t*)ctx->counter.p + (slot & 15);
@@ -133,7 +153,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
 
   CK(cudaMemsetAsync(a.work_counter, 0, 4, st));
   if (slot == 0) CK(cudaEventRecord(ctx->ev[2], st));
-  icp_pair_kernel<<<grid, kThreads, smem, st>>>(a);
+  if (use_l2) icp_pair_l2_kernel<<<grid, threads, 0, st>>>(a);
+  else icp_pair_kernel<<<grid, threads, smem, st>>>(a);
   CK(cudaGetLastError());
   ctx->info.n_launches += 1;
   if (best_of) {
@@ -145,10 +166,10 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   }
   CK(cudaEventRecord(ctx->ev[3], st));
   ctx->timed = true; ctx->timed_stream = (void*)st;
-  cudaFuncAttributes fa;
-  CK(cudaFuncGetAttributes(&fa, icp_pair_kernel));
-  ctx->info.grid = grid; ctx->info.block = kThreads; ctx->info.smem_bytes = (int)smem;
-  ctx->info.regs_per_thread = fa.numRegs; ctx->info.blocks_per_sm = occ; ctx->info.kernel_variant = 0;
+  cudaFuncAttributes fa = fa_on;
+  if (use_l2) CK(cudaFuncGetAttributes(&fa, icp_pair_l2_kernel));
+  ctx->info.grid = grid; ctx->info.block = threads; ctx->info.smem_bytes = (int)(smem + fa.sharedSizeBytes);
+  ctx->info.regs_per_thread = fa.numRegs; ctx->info.blocks_per_sm = occ; ctx->info.kernel_variant = use_l2 ? 1 : 0;
   ctx->info.sm_count = ctx->sm_count;
   return CCICP_OK;
 }
@@ -200,6 +221,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   ccicp_ctx* ctx = new (std::nothrow) ccicp_ctx();
   if (!ctx) return CCICP_E_NOMEM;
   ctx->device = device;
+  { const char* e = getenv("CCICP_FORCE_L2"); ctx->force_l2 = e && e[0] == '1'; }
   cudaDeviceProp prop;
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
     delete ctx; cudaGetLastError(); return CCICP_E_CUDA;
@@ -222,7 +244,7 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   if (!ctx) return CCICP_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
+  DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);

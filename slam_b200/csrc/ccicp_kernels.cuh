@@ -28,8 +28,13 @@
 
 namespace ccicp {
 
-constexpr int kThreads = 256;
-constexpr int kWarps = kThreads / 32;
+// Two instantiations of the same pair kernel (template <kThreads, kGlobal>):
+//   on-chip : 256 threads, the pair's working set in dynamic shared memory (scans up to ~6000 points per cloud)
+//   L2      : 768 threads, one CTA per SM, the working set in a per-CTA global workspace that stays L2/L1-resident
+//             (scans up to CCICP_MAX_POINTS; config C4 = 32768 points per cloud)
+constexpr int kThreadsOnChip = 256;
+constexpr int kThreadsL2 = 768;
+constexpr int kRedStride = 10;     // doubles per warp in the reduction scratch (8 sums + 2 ints)
 constexpr unsigned kNoSlot = 0xFFFFu;
 
 struct GridP {          // per class
@@ -46,6 +51,7 @@ struct IcpArgs {
   int32_t* corr_idx;             // may be NULL
   int32_t* work_counter;
   char* scratch; size_t scratch_per_cta;   // tie-replay trees
+  char* workspace; size_t workspace_per_cta;   // L2 variant: the carved working set of every resident CTA
   int32_t n_pairs, n_seeds, seeds_per_item, items_per_pair;
   int32_t pair_base;             // this launch registers pairs [pair_base, pair_base + n_pairs)
   int32_t max_iter; uint32_t flags;
@@ -57,12 +63,17 @@ struct IcpArgs {
 
 // cells per side for a class of n model points (0 = class never searched,
 // icpPointToPoint.cpp:59,93 skip a class whose model has <= 3 points)
+#ifndef CCICP_GHUGE
+#define CCICP_GHUGE 256    // cells per side for classes with > 8192 model points (L2 variant only)
+#endif
 __host__ __device__ inline int grid_side(int n) {
   if (n <= 3) return 0;
   if (n <= 32) return 8;
   if (n <= 128) return 16;
   if (n <= 512) return 32;
-  return CCICP_GBIG;
+  if (n <= 2048) return CCICP_GBIG;
+  if (n <= 8192) return 128;
+  return CCICP_GHUGE;
 }
 
 __device__ __forceinline__ int f2ord(float f) {   // monotone float -> int
@@ -79,9 +90,9 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
-// ---- shared memory carve-up ------------------------------------------------
+// ---- working-set carve-up (dynamic shared memory, or the CTA's global workspace) ---
 struct Smem {
-  double2* scene;      // [scap]   (aliased during the grid build by tmp_pts / tmp_cell / tmp_rank)
+  const double2* scene;// [scap]   scene points (on-chip: a copy in shared memory; L2 variant: the input array itself)
   float2* mpts;        // [mcap]   model points, float, sorted by cell
   uint16_t* slots;     // [scap]   matched sorted-slot per scene point, kNoSlot = none
   uint16_t* morig;     // [mcap]   sorted slot -> per-class original model index
@@ -89,17 +100,19 @@ struct Smem {
   uint16_t* kind;      // [mcap]   tie replay: the reference kd-tree's index permutation (built lazily)
   uint16_t* cstart;    // [ccap+2] cell -> first sorted slot (exclusive prefix), packed counters while building
   uint32_t* tiebits;   // [scap/32] scene points whose float minimum is shared (tie replay work list)
-  double* red;         // [2][kWarps*10] double-buffered by iteration parity
-  double* rtprev;      // [8] pre-update R,t of the last successful iteration
-  GridP* grid;         // [2]
-  int* misc;           // [16]
+  char* region0;       // scene copy (on-chip) aliased with the sort temporaries tmp_pts / tmp_cell / tmp_rank
+  double* red;         // [2][kWarps*kRedStride] double-buffered by iteration parity   (always shared memory)
+  double* rtprev;      // [8] pre-update R,t of the last successful iteration          (always shared memory)
+  GridP* grid;         // [2]                                                          (always shared memory)
+  int* misc;           // [16]                                                         (always shared memory)
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-__host__ __device__ inline size_t smem_bytes(int mcap, int scap, int ccap) {
-  size_t region0 = (size_t)scap * 16;
-  size_t need_tmp = (size_t)mcap * 12;
+// bytes of the carved working set; global_ws = L2 variant (no scene copy)
+__host__ __device__ inline size_t workset_bytes(int mcap, int scap, int ccap, bool global_ws) {
+  size_t region0 = global_ws ? 0 : (size_t)scap * 16;
+  size_t need_tmp = (size_t)mcap * 14;
   if (need_tmp > region0) region0 = need_tmp;
   size_t b = align_up(region0, 16);
   b += align_up((size_t)mcap * 8, 16);
@@ -107,34 +120,34 @@ __host__ __device__ inline size_t smem_bytes(int mcap, int scap, int ccap) {
   b += 3 * align_up((size_t)mcap * 2, 16);
   b += align_up((size_t)(ccap + 4) * 2, 16);
   b += align_up((size_t)(scap / 32 + 1) * 4, 16);
-  b += (2 * kWarps * 10 + 8) * 8;
-  b += 2 * sizeof(GridP);
-  b += 16 * 4;
-  return b;
+  return align_up(b, 128);
 }
 
-__device__ __forceinline__ Smem carve(char* base, int mcap, int scap, int ccap) {
+template <bool kGlobal>
+__device__ __forceinline__ Smem carve(char* base, int mcap, int scap, int ccap, double* red, double* rtprev, GridP* grid,
+                                      int* misc) {
   Smem s;
-  size_t region0 = (size_t)scap * 16;
-  size_t need_tmp = (size_t)mcap * 12;
+  size_t region0 = kGlobal ? 0 : (size_t)scap * 16;
+  size_t need_tmp = (size_t)mcap * 14;
   if (need_tmp > region0) region0 = need_tmp;
   size_t o = 0;
-  s.scene = (double2*)(base + o); o += align_up(region0, 16);
+  s.region0 = base + o; s.scene = (const double2*)(base + o); o += align_up(region0, 16);
   s.mpts = (float2*)(base + o); o += align_up((size_t)mcap * 8, 16);
   s.slots = (uint16_t*)(base + o); o += align_up((size_t)scap * 2, 16);
   s.morig = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
   s.kinv = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
   s.kind = (uint16_t*)(base + o); o += align_up((size_t)mcap * 2, 16);
   s.cstart = (uint16_t*)(base + o); o += align_up((size_t)(ccap + 4) * 2, 16);
-  s.tiebits = (uint32_t*)(base + o); o += align_up((size_t)(scap / 32 + 1) * 4, 16);
-  s.red = (double*)(base + o); o += 2 * kWarps * 10 * 8;
-  s.rtprev = (double*)(base + o); o += 8 * 8;
-  s.grid = (GridP*)(base + o); o += 2 * sizeof(GridP);
-  s.misc = (int*)(base + o);
-  // tell the compiler these are shared-memory addresses so it emits LDS/STS, not generic LD/ST
-  __builtin_assume(__isShared(s.scene)); __builtin_assume(__isShared(s.mpts)); __builtin_assume(__isShared(s.slots));
-  __builtin_assume(__isShared(s.morig)); __builtin_assume(__isShared(s.kinv)); __builtin_assume(__isShared(s.kind)); __builtin_assume(__isShared(s.cstart)); __builtin_assume(__isShared(s.red)); __builtin_assume(__isShared(s.tiebits));
-  __builtin_assume(__isShared(s.rtprev)); __builtin_assume(__isShared(s.grid)); __builtin_assume(__isShared(s.misc));
+  s.tiebits = (uint32_t*)(base + o);
+  s.red = red; s.rtprev = rtprev; s.grid = grid; s.misc = misc;
+  if (!kGlobal) {
+    // tell the compiler these are shared-memory addresses so it emits LDS/STS, not generic LD/ST
+    __builtin_assume(__isShared(s.scene)); __builtin_assume(__isShared(s.region0)); __builtin_assume(__isShared(s.mpts));
+    __builtin_assume(__isShared(s.slots)); __builtin_assume(__isShared(s.morig)); __builtin_assume(__isShared(s.kinv));
+    __builtin_assume(__isShared(s.kind)); __builtin_assume(__isShared(s.cstart)); __builtin_assume(__isShared(s.tiebits));
+  }
+  __builtin_assume(__isShared(s.red)); __builtin_assume(__isShared(s.rtprev)); __builtin_assume(__isShared(s.grid));
+  __builtin_assume(__isShared(s.misc));
   return s;
 }
 
@@ -162,7 +175,8 @@ struct NNQuery {
   const uint16_t* cs;
 };
 
-__device__ __forceinline__ void nn_search(const float2* __restrict__ mpts, const uint16_t* __restrict__ cstart,
+// (no __restrict__/__ldg on mpts/cstart: in the L2 variant they are global memory written earlier by this kernel)
+__device__ __forceinline__ void nn_search(const float2* mpts, const uint16_t* cstart,
                                           const GridP& g, float qx, float qy, float gate_f, unsigned warm,
                                           float& best, int& bslot, int& tie) {
   best = CUDART_INF_F; bslot = -1;

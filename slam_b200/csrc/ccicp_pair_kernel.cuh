@@ -6,13 +6,15 @@ namespace ccicp {
 
 // ---- grid build: counting (single-digit radix) sort of the model on cell id -
 // a1 (icp.cpp:51-60): model doubles are rounded to float once, here.
+template <int kThreads>
 __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int m0, int nGA, int nNGA, int tid) {
+  constexpr int kWarps = kThreads / 32;
   const int nm = nGA + nNGA;
   const int G0 = grid_side(nGA), G1 = grid_side(nNGA);
   const int ncell = G0 * G0 + G1 * G1;
-  float2* tmp_pts = (float2*)s.scene;
-  uint16_t* tmp_cell = (uint16_t*)(tmp_pts + a.mcap);
-  uint16_t* tmp_rank = tmp_cell + a.mcap;
+  float2* tmp_pts = (float2*)s.region0;
+  uint32_t* tmp_cell = (uint32_t*)(tmp_pts + a.mcap);
+  uint16_t* tmp_rank = (uint16_t*)(tmp_cell + a.mcap);
   uint32_t* cnt32 = (uint32_t*)s.cstart;
   for (int j = tid; j < (ncell + 4) / 2; j += kThreads) cnt32[j] = 0u;
   if (tid < 8) s.misc[M_BBOX + tid] = (tid & 2) ? INT_MIN : INT_MAX;
@@ -73,7 +75,7 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
     const int cell = g.base + iy * g.G + ix;
     const int sh = (cell & 1) * 16;
     uint32_t old = atomicAdd(&cnt32[cell >> 1], 1u << sh);
-    tmp_cell[i] = (uint16_t)cell;
+    tmp_cell[i] = (uint32_t)cell;
     tmp_rank[i] = (uint16_t)((old >> sh) & 0xffffu);
   }
   __syncthreads();
@@ -95,7 +97,7 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
     if ((tid & 31) == 31) wtot[tid >> 5] = incl;
     __syncthreads();
     uint32_t woff = 0;
-    for (int w = 0; w < (tid >> 5); w++) woff += wtot[w];
+    for (int w = 0; w < kWarps; w++) woff += (w < (tid >> 5)) ? wtot[w] : 0u;
     uint32_t run = woff + incl - sum;
     for (int j = beg; j < end; j++) { uint32_t c = s.cstart[j]; s.cstart[j] = (uint16_t)run; run += c; }
   }
@@ -132,6 +134,7 @@ __host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
 // Tied queries are listed in s.tiebits.  Thread c (c = 0 GA, 1 NGA) replays the tied queries of its class one
 // after the other on the class's lazily materialised reference kd-tree (kdreplay.h): the partition work is
 // sequential by definition, and ties are rare (about 1e-7 per query on scan data), so latency is what counts.
+template <int kThreads>
 __device__ __noinline__ void replay_ties(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid) {
   __syncthreads();
   if (tid < 2 && s.grid[tid].G > 0) {
@@ -184,6 +187,7 @@ __device__ __forceinline__ void accum_corr(double (&v)[8], const float2 m, float
 }
 
 // partial sums recomputed from slots[] (used after a tie replay)
+template <int kThreads>
 __device__ __forceinline__ void sums_from_slots(const Smem& s, const double* Rt, int ns, int tid, double pcx, double pcy,
                                                 double (&v)[8], int& cnt) {
 #pragma unroll

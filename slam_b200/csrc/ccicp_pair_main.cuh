@@ -8,7 +8,7 @@ namespace ccicp {
 
 // block-wide sum of up to NV doubles per thread (+ two ints); result broadcast
 // to every thread in a fixed order (deterministic run to run).
-template <int NV>
+template <int NV, int kWarps>
 __device__ __forceinline__ void block_reduce(double* red, int off, double (&v)[NV], int tid) {
 #pragma unroll
   for (int k = 0; k < NV; k++) v[k] = warp_sum(v[k]);
@@ -60,9 +60,16 @@ __device__ __forceinline__ double solve_and_compose(const double* H, const doubl
   return nr > nt ? nr : nt;
 }
 
-__global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(const IcpArgs a) {
+template <int kThreads, bool kGlobal>
+__device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
+  constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
-  const Smem s = carve(smem_raw, a.mcap, a.scap, a.ccap);
+  __shared__ double red_s[2 * kWarps * kRedStride];
+  __shared__ double rtprev_s[8];
+  __shared__ GridP grid_s[2];
+  __shared__ int misc_s[16];
+  char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
+  Smem s = carve<kGlobal>(base, a.mcap, a.scap, a.ccap, red_s, rtprev_s, grid_s, misc_s);
   const int tid = threadIdx.x;
   const float gate_f = __double2float_ru(a.indist);
   const bool replay_on = !(a.flags & CCICP_F_NO_TIE_REPLAY);
@@ -84,10 +91,15 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
     const bool model_ok = nmGA + nmNGA >= 5, scene_ok = ns >= 5;
 
     if (model_ok && scene_ok) {
-      build_grid(a, s, m0, nmGA, nmNGA, tid);
+      build_grid<kThreads>(a, s, m0, nmGA, nmNGA, tid);
       const double2* src = (const double2*)a.scene_xy + s0;
-      for (int i = tid; i < ns; i += kThreads) s.scene[i] = __ldg(src + i);
-      // each thread only ever reads back the scene points it loaded itself
+      if (kGlobal) {
+        s.scene = src;             // read the (L2-resident) input in place every iteration
+      } else {
+        double2* dst = (double2*)s.region0;
+        for (int i = tid; i < ns; i += kThreads) dst[i] = __ldg(src + i);
+        // each thread only ever reads back the scene points it loaded itself
+      }
     }
 
     for (int seed = seed0; seed < seed1; seed++) {
@@ -111,7 +123,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
         const GridP& gp = s.grid[nmNGA >= nmGA];
         const double pcx = (double)gp.cx, pcy = (double)gp.cy;     // pivot of the shifted sums
         for (int iter = 0; iter < a.max_iter; iter++) {
-          double* red = s.red + (iter & 1) * (kWarps * 10);
+          double* red = s.red + (iter & 1) * (kWarps * kRedStride);
           // ---- a4..a6: transform, nearest neighbour, gate; shifted sums of the accepted pairs
           int pend = 0;
           for (int i = tid; i < ns; i += kThreads) {          // loop A: search only (few live registers)
@@ -132,23 +144,23 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
           }
           double v[8];
           int cnt;
-          sums_from_slots(s, Rt, ns, tid, pcx, pcy, v, cnt);        // loop B: converged accumulation
+          sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);        // loop B: converged accumulation
           {
             const int wc = __reduce_add_sync(0xffffffffu, cnt);
             const int wt = __any_sync(0xffffffffu, pend != 0);
             if ((tid & 31) == 0) { int* ip = (int*)&red[(tid >> 5) * 10 + 8]; ip[0] = wc; ip[1] = wt; }
           }
-          block_reduce<8>(red, 0, v, tid);
+          block_reduce<8, kWarps>(red, 0, v, tid);
           int n = 0, any_tie = 0;
 #pragma unroll
           for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&red[w * 10 + 8]; n += ip[0]; any_tie |= ip[1]; }
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
-            replay_ties(a, s, Rt, ns, nsGA, tid);
+            replay_ties<kThreads>(a, s, Rt, ns, nsGA, tid);
             status |= CCICP_ST_TIE_REPLAY;
-            sums_from_slots(s, Rt, ns, tid, pcx, pcy, v, cnt);
+            sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);
             const int wc = __reduce_add_sync(0xffffffffu, cnt);
             if ((tid & 31) == 0) { int* ip = (int*)&red[(tid >> 5) * 10 + 8]; ip[0] = wc; ip[1] = 0; }
-            block_reduce<8>(red, 0, v, tid);
+            block_reduce<8, kWarps>(red, 0, v, tid);
             n = 0;
 #pragma unroll
             for (int w = 0; w < kWarps; w++) n += ((const int*)&red[w * 10 + 8])[0];
@@ -235,7 +247,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
             v[4] += dx; v[5] += dy; v[6] += -y * dx + x * dy;
           }
         }
-        block_reduce<7>(s.red, 0, v, tid);
+        block_reduce<7, kWarps>(s.red, 0, v, tid);
         const double nn = (double)num_corr;
         score = v[0] / nn;
         if (want_info) {
@@ -258,7 +270,7 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
             const double tx = (ax - bx - D0 + y * D2), ty = (ay - by - D1 - x * D2);
             ss[0] += tx * tx + ty * ty;
           }
-          block_reduce<1>(s.red, 8, ss, tid);
+          block_reduce<1, kWarps>(s.red, 8, ss, tid);
           const double sconst = 1.0 / (ss[0] / (double)(2 * num_corr - 3));
           if (!(sch != 0.0) || !(ss[0] > 0.0)) status |= CCICP_ST_INFO_SINGULAR;
           info[0] = nn * sconst; info[1] = 0.0 * sconst; info[2] = -sy * sconst;
@@ -281,6 +293,15 @@ __global__ void __launch_bounds__(kThreads, CCICP_MIN_BLOCKS) icp_pair_kernel(co
       }
     }
   }
+}
+
+__global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsOnChip, false>(a);
+}
+
+// Large scans (config C4): same algorithm, working set in the CTA's global workspace (L2/L1 resident).
+__global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsL2, true>(a);
 }
 
 // best-of-seeds: one warp per pair, arg-min of score over seeds with

@@ -1,0 +1,75 @@
+"""GPU parity of the L2 (global-workspace) variant of the pair kernel: config C4 (32768-point dense slices,
+SURVEY.md 8(d)) and, with CCICP_FORCE_L2=1, the ordinary 1081-beam pairs routed through the same variant."""
+import os
+
+import numpy as np
+import pytest
+
+from slam_b200 import capi, scangen
+from helpers import assert_pose_close, gpu_lockstep_corr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def l2ctx():
+    os.environ["CCICP_FORCE_L2"] = "1"
+    try:
+        c = capi.Context(0)
+    finally:
+        del os.environ["CCICP_FORCE_L2"]
+    yield c
+    c.close()
+
+
+def test_forced_l2_matches_oracle_and_onchip(ctx, l2ctx, oracle):
+    b = scangen.generate(1000, 24)
+    prm = capi.fixed_iter_params(30, flags=capi.F_INFO)
+    args = (b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm)
+    r_on, c_on = ctx.register_batch(*args, want_corr=True)
+    r_l2, c_l2 = l2ctx.register_batch(*args, want_corr=True)
+    assert ctx.launch_info().kernel_variant == 0 and l2ctx.launch_info().kernel_variant == 1
+    assert (c_on == c_l2).all() and (r_on["num_corr"] == r_l2["num_corr"]).all()
+    assert_pose_close(np.c_[r_l2["R"], r_l2["t"]], np.c_[r_on["R"], r_on["t"]], "l2 vs on-chip")
+    for p in range(0, 24, 6):
+        tr = oracle.trace(*b.pair(p), b.init_Rt()[p], max_iter=30, min_delta=-2.0)
+        so = b.scene_off
+        assert (c_l2[0, so[2 * p]:so[2 * p + 2]] == tr["corr"][-1]).all()
+        assert_pose_close(np.r_[r_l2[p]["R"], r_l2[p]["t"]], tr["Rt"], "l2 pair %d" % p)
+
+
+def test_forced_l2_lockstep_with_ties(l2ctx, oracle):
+    """Lattice model: many exact float ties -> the kd-tree replay runs on the global workspace."""
+    g = np.arange(12, dtype=np.float64) * 0.5
+    model = np.stack(np.meshgrid(g, g), -1).reshape(-1, 2)
+    scene = model + 0.25                           # every query equidistant from 4 lattice points
+    pair = (model[:40], model[40:], scene[:40], scene[40:])
+    Rt0 = np.array([1.0, 0, 0, 1, 0, 0])
+    tr = oracle.trace(*pair, Rt0, max_iter=3, min_delta=-2.0)
+    corr, res = gpu_lockstep_corr(l2ctx, pair, tr["Rt_trace"][:-1])
+    assert (corr == tr["corr"]).all()
+    assert (res["status"] & capi.ST_TIE_REPLAY).any()
+
+
+def test_c4_dense_pair(ctx, oracle):
+    """Config C4: one 32768-beam pair (does not fit shared memory -> L2 variant), 30 fixed iterations."""
+    b = scangen.generate(5000, 2, config=4)
+    assert b.max_model > 30000
+    prm = capi.fixed_iter_params(30)
+    res, corr = ctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm, want_corr=True)
+    assert ctx.launch_info().kernel_variant == 1
+    for p in range(2):
+        tr = oracle.trace(*b.pair(p), b.init_Rt()[p], max_iter=30, min_delta=-2.0)
+        so = b.scene_off
+        got, want = corr[0, so[2 * p]:so[2 * p + 2]], tr["corr"][-1]
+        assert (got == want).all(), "pair %d: %d of %d indices differ" % (p, (got != want).sum(), len(want))
+        assert res[p]["num_corr"] == tr["ncorr"][-1]
+        assert_pose_close(np.r_[res[p]["R"], res[p]["t"]], tr["Rt"], "C4 pair %d" % p)
+
+
+def test_c4_lockstep_first_iterations(ctx, oracle):
+    b = scangen.generate(5100, 1, config=4)
+    tr = oracle.trace(*b.pair(0), b.init_Rt()[0], max_iter=4, min_delta=-2.0)
+    corr, res = gpu_lockstep_corr(ctx, b.pair(0), tr["Rt_trace"][:-1])
+    assert (corr == tr["corr"]).all(), "index mismatch in %d entries" % (corr != tr["corr"]).sum()
+    assert (res["num_corr"] == tr["ncorr"]).all()
