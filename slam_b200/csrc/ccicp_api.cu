@@ -25,6 +25,7 @@ struct ccicp_ctx {
   cudaEvent_t chunk_ev[16] = {};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
   bool timed = false, timed_copies = false;
+  int stage_kb = 200;         // CCICP_STAGE_KB
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the L2 variant
   void* timed_stream = nullptr;
   DevBuf counter, scratch, all_results, workspace;
@@ -92,8 +93,12 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
   int occ = 0;
   if (use_l2) {
-    smem = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_l2_kernel, threads, 0));
+    // dynamic shared memory of the L2 variant = staging arrays of the cooperative tie replay (float + u16 per element);
+    // what is left of the SM's 256 KB stays L1 cache for the workspace
+    a.stage_cap = (ctx->stage_kb * 1024 / 6) & ~31;
+    smem = (size_t)a.stage_cap * 6;
+    CK(cudaFuncSetAttribute(icp_pair_l2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_l2_kernel, threads, smem));
   } else {
     CK(cudaFuncSetAttribute(icp_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_kernel, threads, smem));
@@ -153,7 +158,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
 
   CK(cudaMemsetAsync(a.work_counter, 0, 4, st));
   if (slot == 0) CK(cudaEventRecord(ctx->ev[2], st));
-  if (use_l2) icp_pair_l2_kernel<<<grid, threads, 0, st>>>(a);
+  if (use_l2) icp_pair_l2_kernel<<<grid, threads, smem, st>>>(a);
   else icp_pair_kernel<<<grid, threads, smem, st>>>(a);
   CK(cudaGetLastError());
   ctx->info.n_launches += 1;
@@ -222,6 +227,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   if (!ctx) return CCICP_E_NOMEM;
   ctx->device = device;
   { const char* e = getenv("CCICP_FORCE_L2"); ctx->force_l2 = e && e[0] == '1'; }
+  { const char* e = getenv("CCICP_STAGE_KB"); if (e && atoi(e) >= 1 && atoi(e) <= 216) ctx->stage_kb = atoi(e); }
   cudaDeviceProp prop;
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
     delete ctx; cudaGetLastError(); return CCICP_E_CUDA;

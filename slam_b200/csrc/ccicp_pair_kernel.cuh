@@ -174,6 +174,84 @@ __device__ __noinline__ void replay_ties(const IcpArgs& a, const Smem& s, const 
   __syncthreads();
 }
 
+// ---- cooperative tie replay (L2 variant): the whole CTA walks the tied queries one at a time --------------
+template <int kThreads>
+struct CtaCoop {
+  int tid, nt;
+  float* sv; uint16_t* si; int cap; int* bcast;
+  float* fred;                        // [kThreads/32][8] shared
+  __device__ __forceinline__ void sync() { __syncthreads(); }
+  __device__ __forceinline__ void minmax4(float* lo, float* hi) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+        hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+      }
+    }
+    __syncthreads();
+    if ((tid & 31) == 0) {
+#pragma unroll
+      for (int k = 0; k < 4; k++) { fred[(tid >> 5) * 8 + k] = lo[k]; fred[(tid >> 5) * 8 + 4 + k] = hi[k]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      float l = fred[k], h = fred[4 + k];
+      for (int w = 1; w < kThreads / 32; w++) { l = fminf(l, fred[w * 8 + k]); h = fmaxf(h, fred[w * 8 + 4 + k]); }
+      lo[k] = l; hi[k] = h;
+    }
+  }
+};
+
+template <int kThreads>
+__device__ __noinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid,
+                                              char* stage, int stage_cap, float* fred) {
+  __syncthreads();
+  for (int cls = 0; cls < 2; cls++) {
+    if (s.grid[cls].G == 0) continue;
+    const GridP g = s.grid[cls];
+    kdreplay::LNode* nodes = (kdreplay::LNode*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta) + 2 * g.first + 8 * cls;
+    const int max_nodes = 2 * g.n + 8;
+    const SmemPts pts{s.mpts, s.kinv + g.first};
+    uint16_t* ind = s.kind + g.first;
+    CtaCoop<kThreads> co;
+    co.tid = tid; co.nt = kThreads; co.cap = stage_cap;
+    co.sv = (float*)stage; co.si = (uint16_t*)(stage + (size_t)stage_cap * 4);
+    co.bcast = &s.misc[15]; co.fred = fred;
+    int* nn = &s.misc[M_NNODE + cls];
+    int state = s.misc[M_TREE + cls];
+    const int i0 = cls ? nsGA : 0, i1 = cls ? ns : nsGA;
+    for (int w = i0 >> 5; w <= (i1 - 1) >> 5 && i1 > i0; w++) {
+      uint32_t bits = s.tiebits[w];
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int i = (w << 5) + b;
+        if (i < i0 || i >= i1) continue;
+        if (state == 0) state = (kdreplay::lazy_init_coop(pts, g.n, ind, nodes, nn, co) == kdreplay::OK) ? 1 : 2;
+        if (state != 1) continue;                  // tree unavailable: keep the grid's answer
+        const double2 sp = s.scene[i];
+        float qx, qy;
+        transform(Rt, sp.x, sp.y, qx, qy);
+        int32_t o = -1; float d = 0.0f;
+        const int rc = kdreplay::lazy_nearest_coop(pts, ind, nodes, max_nodes, nn, qx, qy, &o, &d, co);
+        if (rc != kdreplay::OK || o < 0) { state = 2; continue; }
+        if (tid == 0) { s.slots[i] = s.kinv[g.first + o]; s.misc[M_REPLAYS] += 1; }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      s.misc[M_TREE + cls] = state;
+      if (state == 2) s.misc[M_TREEFAIL] |= 1;
+    }
+  }
+  __syncthreads();
+  for (int w = tid; w <= (ns - 1) >> 5; w += kThreads) s.tiebits[w] = 0u;
+  __syncthreads();
+}
+
 // Shifted one-pass statistics (a7).  With pivot c (centre of the model's bounding box) every thread
 // accumulates  S_m = sum(m - c), S_t = sum(q - c), P = sum (q - c)(m - c)^T ; then
 //   mu_m = c + S_m/n, mu_t = c + S_t/n, H = P - n (S_t/n)(S_m/n)^T

@@ -65,7 +65,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
   __shared__ double red_s[2 * kWarps * kRedStride];
-  __shared__ double rtprev_s[8];
+  __shared__ double rtprev_s[8 + (kGlobal ? kWarps * 4 : 0)];     // + float[kWarps][8] min/max scratch of the tie replay
   __shared__ GridP grid_s[2];
   __shared__ int misc_s[16];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
@@ -134,7 +134,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, s.slots[i], best, bslot, tie);
+              nn_search<kGlobal>(s.mpts, s.cstart, g, qx, qy, gate_f, s.slots[i], best, bslot, tie);
               if (bslot >= 0 && (double)best < a.indist) {
                 slot = (unsigned)bslot;
                 if (tie && replay_on) { pend = 1; atomicOr(&s.tiebits[i >> 5], 1u << (i & 31)); }
@@ -155,7 +155,8 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
 #pragma unroll
           for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&red[w * 10 + 8]; n += ip[0]; any_tie |= ip[1]; }
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
-            replay_ties<kThreads>(a, s, Rt, ns, nsGA, tid);
+            if (kGlobal) replay_ties_coop<kThreads>(a, s, Rt, ns, nsGA, tid, smem_raw, a.stage_cap, (float*)rtprev_s + 16);
+            else replay_ties<kThreads>(a, s, Rt, ns, nsGA, tid);
             status |= CCICP_ST_TIE_REPLAY;
             sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);
             const int wc = __reduce_add_sync(0xffffffffu, cnt);
@@ -221,7 +222,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie);
+              nn_search<kGlobal>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie);
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
             }
             s.slots[i] = (uint16_t)slot;

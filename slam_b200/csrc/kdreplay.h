@@ -399,4 +399,198 @@ KD_FN int lazy_nearest(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n
   return OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Cooperative variant (large scans, L2 kernel): every thread of the CTA runs the SAME traversal on the same
+// query (all control flow is uniform); a node split is shared out: the gather of the cut coordinate and the
+// bounding boxes of the children are data-parallel, only the float mean (a sequential sum, kdtree.cpp:181-186)
+// and the in-order partition (kdtree.cpp:294-317) run on one thread, on a staged copy (`sv`, `si`).
+//
+// `C` (the cooperation policy) provides:
+//   int tid, nt;                      this thread, threads in the group
+//   float* sv; uint16_t* si; int cap; staging arrays for `cap` elements (shared memory on the device)
+//   int* bcast;                       one int visible to the whole group
+//   void sync();                      group barrier (also orders memory)
+//   void minmax4(float* lo, float* hi) group-wide min of lo[0..3] / max of hi[0..3], result in every thread
+// With nt == 1 (host build, tests/host/kdreplay_host.cpp) this is a plain sequential program.
+template <class P, class I, class C>
+KD_FN void coop_boxes(const P& pts, const uint16_t* si, const float* sv, int c, int k0, int k1, C& co, float* tbox) {
+  float lo[4] = {3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f}, hi[4] = {-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f};
+  for (int k = k0 + co.tid; k <= k1; k += co.nt) {
+    const float vc = sv[k];
+    const float vo = coord(pts, (int)si[k], 1 - c);
+    const float x = c == 0 ? vc : vo, y = c == 0 ? vo : vc;
+    lo[0] = x < lo[0] ? x : lo[0]; hi[0] = x > hi[0] ? x : hi[0];
+    lo[1] = y < lo[1] ? y : lo[1]; hi[1] = y > hi[1] ? y : hi[1];
+  }
+  co.minmax4(lo, hi);
+  tbox[0] = lo[0]; tbox[1] = hi[0]; tbox[2] = lo[1]; tbox[3] = hi[1];
+}
+
+template <class P, class I, class C>
+KD_FN int lazy_init_coop(const P& pts, int n, I* ind, LNode* nodes, int* n_nodes, C& co) {
+  for (int i = co.tid; i < n; i += co.nt) ind[i] = (I)i;
+  if (n <= 0) { if (co.tid == 0) *n_nodes = 0; co.sync(); return OK; }
+  float lo[4] = {3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f}, hi[4] = {-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f};
+  for (int i = co.tid; i < n; i += co.nt) {
+    const Pt v = pts(i);
+    lo[0] = v.x < lo[0] ? v.x : lo[0]; hi[0] = v.x > hi[0] ? v.x : hi[0];
+    lo[1] = v.y < lo[1] ? v.y : lo[1]; hi[1] = v.y > hi[1] ? v.y : hi[1];
+  }
+  co.minmax4(lo, hi);
+  if (co.tid == 0) {
+    LNode r;
+    r.l = 0; r.u = n - 1; r.left = r.right = -1;
+    r.cut_val = r.cut_val_left = r.cut_val_right = 0.0f;
+    r.tbox[0] = lo[0]; r.tbox[1] = hi[0]; r.tbox[2] = lo[1]; r.tbox[3] = hi[1];
+    for (int i = 0; i < 4; i++) r.abox[i] = r.tbox[i];
+    r.cut_dim = (n - 1 <= BUCKET) ? LEAF : UNSPLIT;
+    nodes[0] = r;
+    *n_nodes = 1;
+  }
+  co.sync();
+  return OK;
+}
+
+// Splits node `id` (uniform call).  Ranges larger than the staging capacity fall back to the sequential split
+// on thread 0.
+template <class P, class I, class C>
+KD_FN int lazy_split_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n_nodes, int id, C& co) {
+  const LNode nd0 = nodes[id];
+  const int l = nd0.l, u = nd0.u, n = u - l + 1;
+  if (n > co.cap) {
+    if (co.tid == 0) *co.bcast = lazy_split(pts, ind, nodes, max_nodes, n_nodes, id);
+    co.sync();
+    const int rc = *co.bcast;
+    co.sync();
+    return rc;
+  }
+  int c = -1;
+  float maxspread = 0.0f;
+  for (int i = 0; i < 2; i++) {
+    float sprd = nd0.abox[2 * i + 1] - nd0.abox[2 * i];
+    if (sprd > maxspread) { maxspread = sprd; c = i; }
+  }
+  if (c < 0) return ERR_DEGENERATE;
+  float* sv = co.sv;
+  uint16_t* si = co.si;
+  for (int k = co.tid; k < n; k += co.nt) {                 // gather the cut coordinate (data-parallel)
+    const int o = (int)ind[l + k];
+    si[k] = (uint16_t)o;
+    sv[k] = coord(pts, o, c);
+  }
+  co.sync();
+  if (co.tid == 0) {                                        // sequential by definition: float mean + partition
+    float sum = 0.0f;
+    for (int k = 0; k < n; k++) sum += sv[k];
+    const float average = sum / (float)n;
+    int lb = 0, ub = n - 1;
+    while (lb < ub) {
+      if (sv[lb] <= average) {
+        lb++;
+      } else {
+        const uint16_t ti = si[lb]; si[lb] = si[ub]; si[ub] = ti;
+        const float tv = sv[lb]; sv[lb] = sv[ub]; sv[ub] = tv;
+        ub--;
+      }
+    }
+    *co.bcast = (sv[lb] <= average) ? lb : lb - 1;
+  }
+  co.sync();
+  const int m = *co.bcast;                                  // last index (staged numbering) of the left child
+  for (int k = co.tid; k < n; k += co.nt) ind[l + k] = (I)si[k];
+  if (m >= n - 1 || m < 0) {
+    // one side empty: the other child would be the node itself -> the reference recurses forever
+    co.sync();
+    return ERR_DEGENERATE;
+  }
+  if (*n_nodes + 2 > max_nodes) { co.sync(); return ERR_NODES; }
+  float lbox[4], rbox[4];
+  coop_boxes<P, I, C>(pts, si, sv, c, 0, m, co, lbox);
+  coop_boxes<P, I, C>(pts, si, sv, c, m + 1, n - 1, co, rbox);
+  co.sync();                                                // everyone is done with the staging arrays and *n_nodes
+  if (co.tid == 0) {
+    LNode nd = nd0;
+    const int base = *n_nodes;
+    for (int sde = 0; sde < 2; sde++) {
+      LNode ch;
+      ch.l = sde ? l + m + 1 : l; ch.u = sde ? u : l + m; ch.left = ch.right = -1;
+      ch.cut_val = ch.cut_val_left = ch.cut_val_right = 0.0f;
+      for (int i = 0; i < 4; i++) { ch.tbox[i] = sde ? rbox[i] : lbox[i]; ch.abox[i] = nd.abox[i]; }
+      ch.abox[2 * c] = ch.tbox[2 * c]; ch.abox[2 * c + 1] = ch.tbox[2 * c + 1];
+      ch.cut_dim = (ch.u - ch.l <= BUCKET) ? LEAF : UNSPLIT;
+      nodes[base + sde] = ch;
+    }
+    nd.left = base; nd.right = base + 1;
+    nd.cut_val_right = rbox[2 * c];
+    nd.cut_val_left = lbox[2 * c + 1];
+    nd.cut_val = (float)((double)(nd.cut_val_left + nd.cut_val_right) / 2.0);
+    nd.cut_dim = c;
+    nodes[id] = nd;
+    *n_nodes = base + 2;
+  }
+  co.sync();
+  return OK;
+}
+
+// Exact replay of n_nearest(q, 1), executed redundantly (and uniformly) by every thread of the group; only the
+// node splits are shared out.  Same traversal as lazy_nearest().
+template <class P, class I, class C>
+KD_FN int lazy_nearest_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n_nodes,
+                            float qx, float qy, int32_t* idx_out, float* dis_out, C& co) {
+  struct Pending { int node; float extra; };
+  Pending st[STACK];
+  int sp = 0;
+  float ballsize = 1.0e38f;
+  bool have = false;
+  int32_t best = -1;
+  float bestd = 0.0f;
+  *idx_out = -1; *dis_out = 0.0f;
+  if (*n_nodes <= 0) return OK;
+  int cur = 0;
+  for (;;) {
+    while (cur >= 0 && nodes[cur].cut_dim != LEAF) {
+      if (nodes[cur].cut_dim == UNSPLIT) {
+        int rc = lazy_split_coop(pts, ind, nodes, max_nodes, n_nodes, cur, co);
+        if (rc != OK) return rc;
+      }
+      const LNode nd = nodes[cur];
+      float qval = nd.cut_dim == 0 ? qx : qy;
+      int closer, farther;
+      float extra;
+      if (qval < nd.cut_val) { closer = nd.left; farther = nd.right; extra = nd.cut_val_right - qval; }
+      else { closer = nd.right; farther = nd.left; extra = qval - nd.cut_val_left; }
+      if (sp >= STACK) return ERR_DEPTH;
+      st[sp].node = farther; st[sp].extra = extra; sp++;
+      cur = closer;
+    }
+    if (cur >= 0) {
+      const int l = nodes[cur].l, u = nodes[cur].u;
+      for (int i = l; i <= u; i++) {
+        int o = (int)ind[i];
+        const Pt po = pts(o);
+        float dx = po.x - qx;
+        float dis = 0.0f;
+        dis += dx * dx;
+        if (dis > ballsize) continue;
+        float dy = po.y - qy;
+        dis += dy * dy;
+        if (dis > ballsize) continue;
+        have = true; best = o; bestd = dis; ballsize = dis;
+      }
+    }
+    bool found = false;
+    while (sp > 0) {
+      sp--;
+      int far_ = st[sp].node;
+      float extra = st[sp].extra;
+      if (far_ >= 0 && extra * extra < ballsize && lbox_in_range(nodes[far_], qx, qy, ballsize)) {
+        cur = far_; found = true; break;
+      }
+    }
+    if (!found) break;
+  }
+  if (have) { *idx_out = best; *dis_out = bestd; }
+  return OK;
+}
+
 }  // namespace kdreplay

@@ -65,4 +65,34 @@ int kdr_nn_lazy(const double* pts, int n, const float* q, int nq, int32_t* idx, 
   return 0;
 }
 
+
+// Cooperative lazy tree (the L2 kernel's path) run as a one-thread group; `cap` is the staging capacity, so a
+// small value also exercises the sequential fall-back for oversized ranges.
+struct HostCoop {
+  int tid = 0, nt = 1;
+  float* sv; uint16_t* si; int cap; int* bcast;
+  void sync() {}
+  void minmax4(float*, float*) {}
+};
+
+int kdr_nn_lazy_coop(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis, int cap, int* nodes_built) {
+  std::vector<kdreplay::Pt> p(n > 0 ? n : 1);
+  for (int i = 0; i < n; i++) { p[i].x = (float)pts[2 * i]; p[i].y = (float)pts[2 * i + 1]; }
+  std::vector<kdreplay::LNode> nodes(2 * (n > 0 ? n : 1) + 8);
+  std::vector<uint16_t> ind(n > 0 ? n : 1);
+  std::vector<float> sv(cap > 0 ? cap : 1);
+  std::vector<uint16_t> si(cap > 0 ? cap : 1);
+  int nn = 0, bc = 0;
+  HostCoop co; co.sv = sv.data(); co.si = si.data(); co.cap = cap; co.bcast = &bc;
+  kdreplay::PtrPts acc{p.data()};
+  int rc = kdreplay::lazy_init_coop(acc, n, ind.data(), nodes.data(), &nn, co);
+  if (rc != kdreplay::OK) return -1000 - rc;
+  for (int i = 0; i < nq; i++) {
+    rc = kdreplay::lazy_nearest_coop(acc, ind.data(), nodes.data(), (int)nodes.size(), &nn, q[2 * i], q[2 * i + 1], &idx[i], &dis[i], co);
+    if (rc != kdreplay::OK) return -2000 - rc;
+  }
+  if (nodes_built) *nodes_built = nn;
+  return 0;
+}
+
 }

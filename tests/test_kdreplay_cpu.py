@@ -61,3 +61,16 @@ def test_eager_and_lazy_search_match_reference(kd, oracle):
                               dis.ctypes.data_as(P), C.byref(built)) == 0
         assert (idx == ridx).all() and (dis == rdis).all()
         assert built.value <= oracle.tree(pts)[0]        # the lazy tree never holds more nodes than the full one
+
+
+@pytest.mark.parametrize("cap", [1 << 16, 300])
+def test_cooperative_lazy_search_matches_reference(kd, oracle, cap):
+    """The L2 kernel's cooperative split (staged gather, sequential mean + partition, parallel child boxes)."""
+    for pts, q in clouds():
+        n, nq = len(pts), len(q)
+        ridx, rdis = oracle.nn(pts, q)
+        idx = np.full(nq, -7, np.int32); dis = np.zeros(nq, np.float32)
+        built = C.c_int(0)
+        assert kd.kdr_nn_lazy_coop(pts.ctypes.data_as(P), n, q.ctypes.data_as(P), nq, idx.ctypes.data_as(P),
+                                   dis.ctypes.data_as(P), cap, C.byref(built)) == 0
+        assert (idx == ridx).all() and (dis == rdis).all()
