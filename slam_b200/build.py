@@ -17,7 +17,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "slam_b200", "csrc")
 LIB = os.path.join(ROOT, "slam_b200", "lib")
-MIN_BLOCKS = os.environ.get("CCICP_MIN_BLOCKS", "3")
+MIN_BLOCKS = os.environ.get("CCICP_MIN_BLOCKS", "4")   # 64 registers, 4 CTAs/SM: +6 % over 3 CTAs at 80 registers
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
