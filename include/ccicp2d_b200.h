@@ -10,7 +10,7 @@
  * kdtree::KDTree::n_nearest(q,1) (kdtree.cpp:378-391, 515-683),
  * IcpPointToPoint::getEdgeWeight (icpPointToPoint.cpp:233-316) and
  * getNumberCorrespondences (:317-320).  The reference has no FFI of its own;
- * its interface is the C++ class above.  include/ccicp2d/*.h re-declares that
+ * its interface is the C++ class above.  the headers under include/ccicp2d/ re-declare that
  * class on top of this ABI so ccicp2d/src/icpTools.cpp compiles unchanged
  * (see INTEGRATION.md).
  *
@@ -145,6 +145,32 @@ int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds
                                 ccicp_result* d_out, int32_t* d_corr_idx,
                                 int32_t max_model, int32_t max_scene, void* stream);
 int ccicp_stream_sync(ccicp_ctx* ctx, void* stream);
+
+/* ---- the immediate caller, batched: CCICP::doICPMatch(model_GA, model_NGA, scene_GA, scene_NGA, initPose)
+ * (ccicp2d/src/icpTools.cpp:123-218), SURVEY.md 8(f) rank 1.
+ * A pose is geometry_msgs::Pose: position x,y,z + orientation quaternion x,y,z,w.  Per pair:
+ *   R = rot(yaw(init.orientation)), t = (init.x, init.y)                        (icpTools.cpp:168-176)
+ *   fewer than 5 scene points: out = {0,0,0, 0,0,0, 9999}, the reference's sentinel (icpTools.cpp:179-184),
+ *                              status CCICP_ST_TOO_FEW_SCENE, nothing is registered
+ *   otherwise the two calls at icpTools.cpp:187-188 with `params` (the reference passes indist 5 and keeps the
+ *   Icp defaults max_iter 20 / min_delta 1e-6: ccicp_default_params), then
+ *   out.x,y = t; out.z = init.z; out.orientation = quaternion(roll(init), pitch(init), atan2(R10, R00))
+ *                                                                               (icpTools.cpp:195-212)
+ * The yaw/roll/pitch <-> quaternion conversions restate ROS tf (tf::getYaw, tf::Matrix3x3::getEulerYPR,
+ * tf::createQuaternionFromRPY; the reference depends on an un-vendored, un-pinned tf: ccicp2d/package.xml:10-28).
+ * `records` may be NULL; otherwise it receives the per-pair ccicp_result as ccicp_register_batch would.      */
+typedef struct ccicp_pose {
+  double px, py, pz;
+  double qx, qy, qz, qw;
+} ccicp_pose;
+int ccicp_match_batch(ccicp_ctx* ctx, int32_t n_pairs,
+                      const double* model_xy, const int32_t* model_off,
+                      const double* scene_xy, const int32_t* scene_off,
+                      const ccicp_pose* init_pose, const ccicp_params* params,
+                      ccicp_pose* out_pose, ccicp_result* records);
+/* The pose conversions on their own (host arithmetic, exposed for tests and for callers that batch themselves). */
+void ccicp_pose_to_Rt(const ccicp_pose* pose, double* Rt6);
+void ccicp_Rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out);
 
 /* Pinned host memory for callers that want the H2D/D2H copies to overlap. */
 int ccicp_host_alloc(void** out, size_t bytes);

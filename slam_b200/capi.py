@@ -38,7 +38,8 @@ assert RESULT_DTYPE.itemsize == 160
 
 SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror", "ccicp_last_cuda_error",
            "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
-           "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info"]
+           "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_Rt",
+           "ccicp_Rt_to_pose"]
 
 _lib = None
 
@@ -73,6 +74,11 @@ def load():
     lib.ccicp_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     lib.ccicp_host_free.argtypes = [vp]
     lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
+    lib.ccicp_match_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
+    lib.ccicp_pose_to_Rt.argtypes = [vp, vp]
+    lib.ccicp_pose_to_Rt.restype = None
+    lib.ccicp_Rt_to_pose.argtypes = [vp, vp, vp]
+    lib.ccicp_Rt_to_pose.restype = None
     _lib = lib
     return lib
 
@@ -144,6 +150,21 @@ class Context:
         self._check(rc)
         return (out, corr) if want_corr else out
 
+    def match_batch(self, model_xy, model_off, scene_xy, scene_off, init_pose, params, want_records=False):
+        """Batched CCICP::doICPMatch (ccicp_match_batch).  init_pose: float64 [n,7] = x,y,z,qx,qy,qz,qw."""
+        model_off = np.ascontiguousarray(model_off, np.int32)
+        scene_off = np.ascontiguousarray(scene_off, np.int32)
+        n_pairs = (len(model_off) - 1) // 2
+        model_xy = np.ascontiguousarray(model_xy, np.float64)
+        scene_xy = np.ascontiguousarray(scene_xy, np.float64)
+        init_pose = np.ascontiguousarray(init_pose, np.float64).reshape(n_pairs, 7)
+        out = np.zeros((n_pairs, 7), np.float64)
+        rec = np.zeros(n_pairs, RESULT_DTYPE) if want_records else None
+        rc = self.lib.ccicp_match_batch(self.h, n_pairs, _ptr(model_xy), _ptr(model_off), _ptr(scene_xy), _ptr(scene_off),
+                                        _ptr(init_pose), C.byref(params), _ptr(out), _ptr(rec))
+        self._check(rc)
+        return (out, rec) if want_records else out
+
     def register_batch_device(self, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt,
                               params, d_out, d_corr, max_model, max_scene, stream=None):
         """Device-pointer call (ints from tensor.data_ptr()); asynchronous on `stream` (cudaStream_t as int)."""
@@ -177,3 +198,19 @@ def pinned_array(shape, dtype):
 
 
 _PINNED = {}
+
+
+def pose_to_Rt(pose7):
+    """ccicp_pose_to_Rt on one pose (x,y,z,qx,qy,qz,qw) -> [6]."""
+    p = np.ascontiguousarray(pose7, np.float64).reshape(7)
+    out = np.zeros(6, np.float64)
+    load().ccicp_pose_to_Rt(_ptr(p), _ptr(out))
+    return out
+
+
+def Rt_to_pose(Rt6, init_pose7):
+    r = np.ascontiguousarray(Rt6, np.float64).reshape(6)
+    p = np.ascontiguousarray(init_pose7, np.float64).reshape(7)
+    out = np.zeros(7, np.float64)
+    load().ccicp_Rt_to_pose(_ptr(r), _ptr(p), _ptr(out))
+    return out

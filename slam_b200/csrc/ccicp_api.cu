@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "ccicp_pair_main.cuh"
+#include "pose_math.h"
 
 using namespace ccicp;
 
@@ -368,6 +369,41 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   if (n_chunks == 1) CK(cudaStreamSynchronize(st));
   else { CK(cudaStreamSynchronize(ctx->kstream[0])); CK(cudaStreamSynchronize(ctx->kstream[1])); }
   ctx->timed_copies = true;
+  return CCICP_OK;
+}
+
+void ccicp_pose_to_Rt(const ccicp_pose* pose, double* Rt6) {
+  if (pose && Rt6) ccicp_pose_math::pose_to_Rt(*pose, Rt6);
+}
+
+void ccicp_Rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out) {
+  if (Rt6 && init_pose && out) ccicp_pose_math::Rt_to_pose(Rt6, *init_pose, out);
+}
+
+// Batched CCICP::doICPMatch(vectors..., initPose), icpTools.cpp:123-218.
+int ccicp_match_batch(ccicp_ctx* ctx, int32_t n_pairs, const double* model_xy, const int32_t* model_off,
+                      const double* scene_xy, const int32_t* scene_off, const ccicp_pose* init_pose,
+                      const ccicp_params* params, ccicp_pose* out_pose, ccicp_result* records) {
+  if (!ctx || !params || n_pairs < 0) return CCICP_E_INVALID;
+  if (n_pairs == 0) return CCICP_OK;
+  if (!init_pose || !out_pose || !scene_off) return CCICP_E_INVALID;
+  std::vector<double> init;
+  std::vector<ccicp_result> tmp;
+  try {
+    init.resize((size_t)n_pairs * 6);
+    if (!records) tmp.resize((size_t)n_pairs);
+  } catch (const std::bad_alloc&) { return CCICP_E_NOMEM; }
+  for (int32_t p = 0; p < n_pairs; p++) ccicp_pose_math::pose_to_Rt(init_pose[p], &init[(size_t)p * 6]);
+  ccicp_result* rec = records ? records : tmp.data();
+  const int rc = ccicp_register_batch(ctx, n_pairs, 1, model_xy, model_off, scene_xy, scene_off, init.data(), params, rec,
+                                      nullptr);
+  if (rc != CCICP_OK) return rc;
+  for (int32_t p = 0; p < n_pairs; p++) {
+    // the scene check comes first in the reference, before the Icp object exists (icpTools.cpp:179-187)
+    if (scene_off[2 * (size_t)p + 2] - scene_off[2 * (size_t)p] < 5) { ccicp_pose_math::sentinel(&out_pose[p]); continue; }
+    const double Rt[6] = {rec[p].R[0], rec[p].R[1], rec[p].R[2], rec[p].R[3], rec[p].t[0], rec[p].t[1]};
+    ccicp_pose_math::Rt_to_pose(Rt, init_pose[p], &out_pose[p]);
+  }
   return CCICP_OK;
 }
 
