@@ -169,8 +169,8 @@ int ccicp_match_batch(ccicp_ctx* ctx, int32_t n_pairs,
                       const ccicp_pose* init_pose, const ccicp_params* params,
                       ccicp_pose* out_pose, ccicp_result* records);
 /* The pose conversions on their own (host arithmetic, exposed for tests and for callers that batch themselves). */
-void ccicp_pose_to_Rt(const ccicp_pose* pose, double* Rt6);
-void ccicp_Rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out);
+void ccicp_pose_to_rt(const ccicp_pose* pose, double* Rt6);
+void ccicp_rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out);
 
 /* Pinned host memory for callers that want the H2D/D2H copies to overlap. */
 int ccicp_host_alloc(void** out, size_t bytes);

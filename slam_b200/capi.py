@@ -38,8 +38,8 @@ assert RESULT_DTYPE.itemsize == 160
 
 SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror", "ccicp_last_cuda_error",
            "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
-           "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_Rt",
-           "ccicp_Rt_to_pose"]
+           "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_rt",
+           "ccicp_rt_to_pose"]
 
 _lib = None
 
@@ -75,10 +75,10 @@ def load():
     lib.ccicp_host_free.argtypes = [vp]
     lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
     lib.ccicp_match_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
-    lib.ccicp_pose_to_Rt.argtypes = [vp, vp]
-    lib.ccicp_pose_to_Rt.restype = None
-    lib.ccicp_Rt_to_pose.argtypes = [vp, vp, vp]
-    lib.ccicp_Rt_to_pose.restype = None
+    lib.ccicp_pose_to_rt.argtypes = [vp, vp]
+    lib.ccicp_pose_to_rt.restype = None
+    lib.ccicp_rt_to_pose.argtypes = [vp, vp, vp]
+    lib.ccicp_rt_to_pose.restype = None
     _lib = lib
     return lib
 
@@ -201,10 +201,10 @@ _PINNED = {}
 
 
 def pose_to_Rt(pose7):
-    """ccicp_pose_to_Rt on one pose (x,y,z,qx,qy,qz,qw) -> [6]."""
+    """ccicp_pose_to_rt on one pose (x,y,z,qx,qy,qz,qw) -> [6]."""
     p = np.ascontiguousarray(pose7, np.float64).reshape(7)
     out = np.zeros(6, np.float64)
-    load().ccicp_pose_to_Rt(_ptr(p), _ptr(out))
+    load().ccicp_pose_to_rt(_ptr(p), _ptr(out))
     return out
 
 
@@ -212,5 +212,5 @@ def Rt_to_pose(Rt6, init_pose7):
     r = np.ascontiguousarray(Rt6, np.float64).reshape(6)
     p = np.ascontiguousarray(init_pose7, np.float64).reshape(7)
     out = np.zeros(7, np.float64)
-    load().ccicp_Rt_to_pose(_ptr(r), _ptr(p), _ptr(out))
+    load().ccicp_rt_to_pose(_ptr(r), _ptr(p), _ptr(out))
     return out

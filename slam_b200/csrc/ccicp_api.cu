@@ -372,11 +372,11 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   return CCICP_OK;
 }
 
-void ccicp_pose_to_Rt(const ccicp_pose* pose, double* Rt6) {
+void ccicp_pose_to_rt(const ccicp_pose* pose, double* Rt6) {
   if (pose && Rt6) ccicp_pose_math::pose_to_Rt(*pose, Rt6);
 }
 
-void ccicp_Rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out) {
+void ccicp_rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out) {
   if (Rt6 && init_pose && out) ccicp_pose_math::Rt_to_pose(Rt6, *init_pose, out);
 }
 
