@@ -156,6 +156,16 @@ def load_traffic():
         return None
 
 
+def issue_roofline(traffic, k_ms, sms, clocks):
+    if not traffic or not traffic.get("warp_instr_per_launch"):
+        return None
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    peak = sms * 4 * mhz * 1e6                       # 4 schedulers per SM, 1 warp instruction per cycle each
+    ach = traffic["warp_instr_per_launch"] / (k_ms * 1e-3)
+    return {"bound": "issue", "achieved": ach / 1e12, "peak": peak / 1e12, "unit": "T warp-instr/s", "frac": ach / peak,
+            "source": traffic.get("capture")}
+
+
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -270,6 +280,9 @@ def gpu_arm(args, rank, world, local_rank):
                      "kernel": "icp_pair_kernel", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
                      "peak_source": peak_src,
                      "note": "on-chip kernel: HBM is not the binding resource (SURVEY.md 8(d)); see issue_slot_util in profiles/"},
+        # secondary: the resource that actually binds this on-chip kernel is instruction issue;
+        # warp instructions per launch come from the committed ncu capture of the same command, time is live
+        "roofline_issue": issue_roofline(traffic, k_ms, li.sm_count, clocks),
         "kernel": {"grid": li.grid, "block": li.block, "smem_bytes": li.smem_bytes, "regs": li.regs_per_thread,
                    "ctas_per_sm": li.blocks_per_sm, "sms": li.sm_count},
         "clocks": clocks,

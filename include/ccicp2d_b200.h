@@ -172,6 +172,26 @@ int ccicp_match_batch(ccicp_ctx* ctx, int32_t n_pairs,
 void ccicp_pose_to_rt(const ccicp_pose* pose, double* Rt6);
 void ccicp_rt_to_pose(const double* Rt6, const ccicp_pose* init_pose, ccicp_pose* out);
 
+/* ---- the step before the path: GA / NGA classification of segmented obstacle points --------------------
+ * CCICP::classifyPoints (ccicp2d/src/icpTools.cpp:36-103; constants icpTools.h:24-26), SURVEY.md 8(f) rank 2,
+ * batched over clouds.  Per cloud:
+ *   - every point is binned on a 1200 x 1200 grid of 0.5 m cells centred on the origin:
+ *       bind = floor(((double)coord + 300.0) / 0.5); points outside [0,1200) in x or y are dropped (:47-54)
+ *   - the output lists the points bin by bin (bin index x*1200 + y ascending), points of one bin in input order;
+ *     points of the outermost ring of bins are dropped (:72-77) but still count as "occupied" for their neighbours
+ *   - ground_adj = 1 iff at least 2 (GRD_ADJ_THRESH) of the bin's 8 neighbour bins are empty (:79-98)
+ * xyz: float [cloud_off[n_clouds]][3] (PointXYZGD x,y,z); cloud_off: int32 [n_clouds+1] (points).
+ * out_xyz / out_ground_adj / out_src_index (may be NULL; index of the point inside its input cloud) are written
+ * per cloud starting at cloud_off[c]; out_count[c] = points kept for cloud c.  NaN coordinates are dropped
+ * (the reference's float -> int conversion of NaN is undefined).  Host buffers; synchronous.
+ * At most 2048 clouds per call.                                                                              */
+int ccicp_classify_points(ccicp_ctx* ctx, int32_t n_clouds, const float* xyz, const int32_t* cloud_off,
+                          float* out_xyz, uint8_t* out_ground_adj, int32_t* out_src_index, int32_t* out_count);
+/* Same, device-resident buffers, asynchronous on `stream` (NULL = ctx stream). */
+int ccicp_classify_points_device(ccicp_ctx* ctx, int32_t n_clouds, const float* d_xyz, const int32_t* d_cloud_off,
+                                 int64_t n_points, float* d_out_xyz, uint8_t* d_out_ground_adj,
+                                 int32_t* d_out_src_index, int32_t* d_out_count, void* stream);
+
 /* Pinned host memory for callers that want the H2D/D2H copies to overlap. */
 int ccicp_host_alloc(void** out, size_t bytes);
 int ccicp_host_free(void* p);

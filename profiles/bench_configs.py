@@ -52,7 +52,46 @@ def main():
         init = np.concatenate([scangen.pose_to_Rt(scangen.hypotheses(int(s), S)) for s in b.seeds], 0)
         prm5 = capi.fixed_iter_params(30, flags=capi.F_BEST_OF_SEEDS)
         run(ctx, "C5 256 seeds best-of", b, prm5, n_seeds=S, init=init, reps=2)
+    if "classify" in which:
+        bench_classify(ctx, pairs or 256)
     ctx.close()
+
+
+def bench_classify(ctx, n_clouds, pts=70000):
+    """batched classifyPoints, device-resident, CUDA-event timed; numpy oracle timed beside it."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_classify_cpu import synthetic_cloud
+    from oracle import classify_port as cp
+    base = [synthetic_cloud(k, pts) for k in range(8)]
+    clouds = [base[k % 8] for k in range(n_clouds)]
+    xyz = np.concatenate(clouds, 0)
+    off = np.cumsum([0] + [len(c) for c in clouds]).astype(np.int32)
+    n = len(xyz)
+    dev = torch.device("cuda", 0)
+    d_xyz = torch.from_numpy(xyz).to(dev); d_off = torch.from_numpy(off).to(dev)
+    o_xyz = torch.empty_like(d_xyz); o_ga = torch.empty(n, dtype=torch.uint8, device=dev)
+    o_src = torch.empty(n, dtype=torch.int32, device=dev); o_cnt = torch.empty(n_clouds, dtype=torch.int32, device=dev)
+    st = torch.cuda.Stream(device=dev)
+    ms = []
+    for _ in range(6):
+        ctx.classify_points_device(n_clouds, d_xyz.data_ptr(), d_off.data_ptr(), n, o_xyz.data_ptr(), o_ga.data_ptr(),
+                                   o_src.data_ptr(), o_cnt.data_ptr(), st.cuda_stream)
+        ctx.sync(st.cuda_stream)
+        ms.append(ctx.launch_info().last_kernel_ms)
+    k = float(np.min(ms[1:]))
+    t0 = time.perf_counter()
+    for c in base[:4]:
+        cp.classify(c)
+    cpu_pts_s = 4 * pts / (time.perf_counter() - t0)
+    alg = n * (12 + 12 + 1 + 4) + n_clouds * 8            # xyz in; xyz, flag, source index out; offsets + counts
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    print(json.dumps({"config": "classifyPoints", "clouds": n_clouds, "points": n, "ms": k, "points_per_s": n / (k * 1e-3),
+                      "clouds_per_s": n_clouds / (k * 1e-3), "n_launches": ctx.launch_info().n_launches,
+                      "roofline": {"bound": "hbm", "algorithmic_bytes": alg, "achieved": alg / (k * 1e-3) / 1e9, "peak": peak,
+                                   "unit": "GB/s", "frac": alg / (k * 1e-3) / 1e9 / peak},
+                      "cpu_baseline": {"value": cpu_pts_s, "unit": "points/s", "cores": 1, "kind": "port (numpy restatement)"},
+                      "kept_mean": float(o_cnt.float().mean().item())}), flush=True)
 
 
 if __name__ == "__main__":

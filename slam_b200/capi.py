@@ -39,7 +39,7 @@ assert RESULT_DTYPE.itemsize == 160
 SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror", "ccicp_last_cuda_error",
            "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
            "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_rt",
-           "ccicp_rt_to_pose"]
+           "ccicp_rt_to_pose", "ccicp_classify_points", "ccicp_classify_points_device"]
 
 _lib = None
 
@@ -75,6 +75,8 @@ def load():
     lib.ccicp_host_free.argtypes = [vp]
     lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
     lib.ccicp_match_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
+    lib.ccicp_classify_points.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.ccicp_classify_points_device.argtypes = [vp, i32, vp, vp, C.c_int64, vp, vp, vp, vp, vp]
     lib.ccicp_pose_to_rt.argtypes = [vp, vp]
     lib.ccicp_pose_to_rt.restype = None
     lib.ccicp_rt_to_pose.argtypes = [vp, vp, vp]
@@ -164,6 +166,26 @@ class Context:
                                         _ptr(init_pose), C.byref(params), _ptr(out), _ptr(rec))
         self._check(rc)
         return (out, rec) if want_records else out
+
+    def classify_points(self, xyz, cloud_off):
+        """Batched CCICP::classifyPoints.  xyz float32 [N,3], cloud_off int32 [n_clouds+1].
+        Returns a list of (xyz[k,3], ground_adj[k], src_index[k]) per cloud."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        cloud_off = np.ascontiguousarray(cloud_off, np.int32)
+        nc, n = len(cloud_off) - 1, len(xyz)
+        oxyz = np.zeros((max(n, 1), 3), np.float32); oga = np.zeros(max(n, 1), np.uint8)
+        osrc = np.zeros(max(n, 1), np.int32); ocnt = np.zeros(max(nc, 1), np.int32)
+        self._check(self.lib.ccicp_classify_points(self.h, nc, _ptr(xyz), _ptr(cloud_off), _ptr(oxyz), _ptr(oga),
+                                                   _ptr(osrc), _ptr(ocnt)))
+        out = []
+        for c in range(nc):
+            a, k = int(cloud_off[c]), int(ocnt[c])
+            out.append((oxyz[a:a + k].copy(), oga[a:a + k].copy(), osrc[a:a + k].copy()))
+        return out
+
+    def classify_points_device(self, n_clouds, d_xyz, d_off, n_points, d_out_xyz, d_out_ga, d_out_src, d_out_cnt, stream=None):
+        self._check(self.lib.ccicp_classify_points_device(self.h, n_clouds, d_xyz, d_off, n_points, d_out_xyz, d_out_ga,
+                                                          d_out_src or None, d_out_cnt, stream or None))
 
     def register_batch_device(self, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt,
                               params, d_out, d_corr, max_model, max_scene, stream=None):

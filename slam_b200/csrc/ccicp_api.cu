@@ -9,6 +9,7 @@
 
 #include "ccicp_pair_main.cuh"
 #include "pose_math.h"
+#include "classify.cuh"
 
 using namespace ccicp;
 
@@ -31,6 +32,8 @@ struct ccicp_ctx {
   void* timed_stream = nullptr;
   DevBuf counter, scratch, all_results, workspace;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
+  DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap;            // classification scratch
+  DevBuf c_xyz, c_off, c_out_xyz, c_out_ga, c_out_src, c_out_cnt;             // classification, host-buffer path
   ccicp_launch_info info{};
   std::string last_err;
 };
@@ -252,7 +255,9 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
-                    &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr};
+                    &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
+                    &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
+                    &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->chunk_ev) if (ev) cudaEventDestroy(ev);
@@ -404,6 +409,69 @@ int ccicp_match_batch(ccicp_ctx* ctx, int32_t n_pairs, const double* model_xy, c
     const double Rt[6] = {rec[p].R[0], rec[p].R[1], rec[p].R[2], rec[p].R[3], rec[p].t[0], rec[p].t[1]};
     ccicp_pose_math::Rt_to_pose(Rt, init_pose[p], &out_pose[p]);
   }
+  return CCICP_OK;
+}
+
+// GA / NGA classification (CCICP::classifyPoints, icpTools.cpp:36-103), device buffers.
+int ccicp_classify_points_device(ccicp_ctx* ctx, int32_t n_clouds, const float* d_xyz, const int32_t* d_cloud_off,
+                                 int64_t n_points, float* d_out_xyz, uint8_t* d_out_ground_adj, int32_t* d_out_src_index,
+                                 int32_t* d_out_count, void* stream) {
+  if (!ctx || n_clouds < 0 || n_clouds > classify::kMaxClouds || n_points < 0 || n_points > 0xFFFFFFFFll) return CCICP_E_INVALID;
+  if (n_clouds == 0) return CCICP_OK;
+  if (!d_cloud_off || !d_out_count || (n_points > 0 && (!d_xyz || !d_out_xyz || !d_out_ground_adj))) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  int rc;
+  const size_t nb = (size_t)(n_points > 0 ? n_points : 1) * 4;
+  if ((rc = reserve(ctx, ctx->c_keys, nb))) return rc;
+  if ((rc = reserve(ctx, ctx->c_vals, nb))) return rc;
+  if ((rc = reserve(ctx, ctx->c_keys_tmp, nb))) return rc;
+  if ((rc = reserve(ctx, ctx->c_vals_tmp, nb))) return rc;
+  if ((rc = reserve(ctx, ctx->c_hist, classify::hist_words(n_points) * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->c_bitmap, (size_t)n_clouds * classify::kWordsPerCloud * 4))) return rc;
+  classify::Scratch sc{(uint32_t*)ctx->c_keys.p, (uint32_t*)ctx->c_vals.p, (uint32_t*)ctx->c_keys_tmp.p,
+                       (uint32_t*)ctx->c_vals_tmp.p, (uint32_t*)ctx->c_hist.p, (uint32_t*)ctx->c_bitmap.p};
+  CK(cudaEventRecord(ctx->ev[2], st));
+  ctx->info.n_launches = classify::run(d_xyz, d_cloud_off, n_clouds, n_points, sc, d_out_xyz, d_out_ground_adj,
+                                       d_out_src_index, d_out_count, st);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(ctx->ev[3], st));
+  ctx->timed = true; ctx->timed_copies = false; ctx->timed_stream = (void*)st;
+  ctx->info.kernel_variant = 2; ctx->info.block = 256; ctx->info.grid = (int)((n_points + 255) / 256);
+  return CCICP_OK;
+}
+
+int ccicp_classify_points(ccicp_ctx* ctx, int32_t n_clouds, const float* xyz, const int32_t* cloud_off, float* out_xyz,
+                          uint8_t* out_ground_adj, int32_t* out_src_index, int32_t* out_count) {
+  if (!ctx || n_clouds < 0 || n_clouds > classify::kMaxClouds) return CCICP_E_INVALID;
+  if (n_clouds == 0) return CCICP_OK;
+  if (!cloud_off || !out_count || cloud_off[0] != 0) return CCICP_E_INVALID;
+  for (int32_t c = 0; c < n_clouds; c++) if (cloud_off[c + 1] < cloud_off[c]) return CCICP_E_INVALID;
+  const int64_t n = cloud_off[n_clouds];
+  if (n > 0 && (!xyz || !out_xyz || !out_ground_adj)) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t np = (size_t)(n > 0 ? n : 1);
+  if ((rc = reserve(ctx, ctx->c_xyz, np * 12))) return rc;
+  if ((rc = reserve(ctx, ctx->c_off, ((size_t)n_clouds + 1) * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->c_out_xyz, np * 12))) return rc;
+  if ((rc = reserve(ctx, ctx->c_out_ga, np))) return rc;
+  if ((rc = reserve(ctx, ctx->c_out_src, np * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->c_out_cnt, (size_t)n_clouds * 4))) return rc;
+  if (n > 0) CK(cudaMemcpyAsync(ctx->c_xyz.p, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->c_off.p, cloud_off, ((size_t)n_clouds + 1) * 4, cudaMemcpyHostToDevice, st));
+  rc = ccicp_classify_points_device(ctx, n_clouds, (const float*)ctx->c_xyz.p, (const int32_t*)ctx->c_off.p, n,
+                                    (float*)ctx->c_out_xyz.p, (uint8_t*)ctx->c_out_ga.p, (int32_t*)ctx->c_out_src.p,
+                                    (int32_t*)ctx->c_out_cnt.p, (void*)st);
+  if (rc) return rc;
+  if (n > 0) {
+    CK(cudaMemcpyAsync(out_xyz, ctx->c_out_xyz.p, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(out_ground_adj, ctx->c_out_ga.p, (size_t)n, cudaMemcpyDeviceToHost, st));
+    if (out_src_index) CK(cudaMemcpyAsync(out_src_index, ctx->c_out_src.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+  }
+  CK(cudaMemcpyAsync(out_count, ctx->c_out_cnt.p, (size_t)n_clouds * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
   return CCICP_OK;
 }
 
