@@ -92,7 +92,7 @@ struct Scratch {          // device pointers, sized by the caller
   uint32_t *keys, *vals, *keys_tmp, *vals_tmp, *hist, *bitmap;
 };
 
-inline size_t hist_words(int64_t n) { return (size_t)256 * rsort::num_tiles(n) + 16; }
+inline size_t hist_words(int64_t n) { return rsort::hist_words(n); }
 
 // Enqueues the whole classification; returns the number of kernels launched.
 inline int run(const float* d_xyz, const int32_t* d_off, int n_clouds, int64_t n, const Scratch& s, float* d_out_xyz,
