@@ -312,7 +312,7 @@ def main():
         from slam_b200 import scangen
         cores = host_cores()
         batch = scangen.generate(SEED0, min(args.pairs, max(64, cores * 8)), config=1)
-        ppc = args.cpu_pairs_per_core or 8            # ~12 ms each -> ~0.1 s per core per step
+        ppc = args.cpu_pairs_per_core or 48           # ~12 ms each -> ~0.6 s per core per step
         for _ in range(args.warmup):
             cpu_reference_rate(batch, cores, 2)
         vals, walls = [], []
