@@ -42,6 +42,10 @@ def main():
     prm = capi.fixed_iter_params(30)
     if "c2" in which:
         run(ctx, "C2 odometry 1081-beam", scangen.generate(1000, pairs or 4096, config=1), prm)
+    if "c2x" in which:      # bit-identical mode (sequential sums + NR SVD)
+        b2 = scangen.generate(1000, pairs or 4096, config=1, pinned=capi.pinned_array)
+        run(ctx, "C2 default mode (pinned)", b2, prm)
+        run(ctx, "C2 CCICP_F_EXACT_SUMS (pinned)", b2, capi.fixed_iter_params(30, flags=capi.F_EXACT_SUMS))
     if "c3" in which:
         run(ctx, "C3 loop-closure 1081-beam", scangen.generate(10**6, pairs or 16384, config=3), prm)
     if "c4" in which:

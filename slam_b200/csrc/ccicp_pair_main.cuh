@@ -3,6 +3,7 @@
 // iterations of every seed in the chunk, entirely in shared memory/registers.
 #pragma once
 #include "ccicp_pair_kernel.cuh"
+#include "exact_solve.cuh"
 
 namespace ccicp {
 
@@ -60,12 +61,76 @@ __device__ __forceinline__ double solve_and_compose(const double* H, const doubl
   return nr > nt ? nr : nt;
 }
 
+// CCICP_F_EXACT_SUMS: statistics and solve of one fitStep in the reference's evaluation order (exact_solve.cuh).
+// Lanes 0..3 of warp 0 carry the four independent sequential accumulators of each pass; lane 0 runs the SVD.
+// ex[0..3] = mu_m, mu_t; ex[4..7] = H; ex[8..13] = new R,t; ex[14] = delta; ex[15] = status bits.
+__device__ __noinline__ void exact_step(const Smem& s, const double* Rt, int ns, int n, int tid, double* ex) {
+  if (tid < 4) {
+    const int cm = tid & 1, ct = tid >> 1;
+    double acc = 0.0;
+#pragma unroll 4
+    for (int i = 0; i < ns; i++) {                         // icpPointToPoint.cpp:80-86, 115-121 (scene order, GA first)
+      const unsigned slot = s.slots[i];
+      if (slot == kNoSlot) continue;
+      const double2 sp = s.scene[i];
+      float qx, qy;
+      transform(Rt, sp.x, sp.y, qx, qy);
+      const float2 m = s.mpts[slot];
+      const double v = tid < 2 ? (double)(cm ? m.y : m.x) : (double)(cm ? qy : qx);
+      acc += v;
+    }
+    ex[tid] = acc / (double)n;                             // :149-150
+    __syncwarp(0xFu);
+    const double mu_m = ex[cm], mu_t = ex[2 + ct];
+    double h = 0.0;
+#pragma unroll 4
+    for (int i = 0; i < ns; i++) {                         // H[ct][cm] = sum_k (p_t[k][ct]-mu_t[ct]) * (p_m[k][cm]-mu_m[cm])
+      const unsigned slot = s.slots[i];
+      if (slot == kNoSlot) continue;
+      const double2 sp = s.scene[i];
+      float qx, qy;
+      transform(Rt, sp.x, sp.y, qx, qy);
+      const float2 m = s.mpts[slot];
+      const double pt = (double)(ct ? qy : qx), pm = (double)(cm ? m.y : m.x);
+      h += __dmul_rn(pt - mu_t, pm - mu_m);
+    }
+    ex[4 + tid] = h;
+    __syncwarp(0xFu);
+    if (tid == 0) {
+      const double H[4] = {ex[4], ex[5], ex[6], ex[7]};
+      const double mu_m2[2] = {ex[0], ex[1]}, mu_t2[2] = {ex[2], ex[3]};
+      double U[4], V[4];
+      exact::svd2(H, U, V);
+      double R_[4], t_[2], Rn[4], tn[2];
+      for (int i = 0; i < 2; i++)                          // R_ = V * ~U (:162)
+        for (int j = 0; j < 2; j++) { double c = 0.0; for (int k = 0; k < 2; k++) c += V[2 * i + k] * U[2 * j + k]; R_[2 * i + j] = c; }
+      for (int i = 0; i < 2; i++) { double c = 0.0; for (int k = 0; k < 2; k++) c += R_[2 * i + k] * mu_t2[k]; t_[i] = mu_m2[i] - c; }
+      for (int i = 0; i < 2; i++)                          // R = R_*R, t = R_*t + t_ (:166-167)
+        for (int j = 0; j < 2; j++) { double c = 0.0; for (int k = 0; k < 2; k++) c += R_[2 * i + k] * Rt[2 * k + j]; Rn[2 * i + j] = c; }
+      for (int i = 0; i < 2; i++) { double c = 0.0; for (int k = 0; k < 2; k++) c += R_[2 * i + k] * Rt[4 + k]; tn[i] = c + t_[i]; }
+      double nr = 0.0, nt = 0.0;                           // :170, matrix.cpp:354-360
+      for (int i = 0; i < 2; i++) for (int j = 0; j < 2; j++) { const double v = R_[2 * i + j] - (i == j ? 1.0 : 0.0); nr += v * v; }
+      for (int i = 0; i < 2; i++) nt += t_[i] * t_[i];
+      nr = sqrt(nr); nt = sqrt(nt);
+      ex[8] = Rn[0]; ex[9] = Rn[1]; ex[10] = Rn[2]; ex[11] = Rn[3]; ex[12] = tn[0]; ex[13] = tn[1];
+      ex[14] = nr < nt ? nt : nr;
+      const double det = R_[0] * R_[3] - R_[1] * R_[2];
+      const double detH = H[0] * H[3] - H[1] * H[2];
+      uint32_t st = 0;
+      if (det < 0.0) st |= CCICP_ST_REFLECTION;
+      if (detH == 0.0) st |= CCICP_ST_DEGENERATE;
+      ex[15] = (double)st;
+    }
+  }
+}
+
 template <int kThreads, bool kGlobal>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
   __shared__ double red_s[2 * kWarps * kRedStride];
   __shared__ double rtprev_s[8 + (kGlobal ? kWarps * 4 : 0)];     // + float[kWarps][8] min/max scratch of the tie replay
+  __shared__ double exact_s[16];
   __shared__ GridP grid_s[2];
   __shared__ int misc_s[16];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
@@ -185,7 +250,17 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];
           }
           // ---- a8, a9
-          last_delta = solve_and_compose(H, mu_m, mu_t, Rt, status);
+          if (a.flags & CCICP_F_EXACT_SUMS) {
+            __syncthreads();                  // slots of this iteration are final and visible
+            exact_step(s, Rt, ns, n, tid, exact_s);
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < 6; q++) Rt[q] = exact_s[8 + q];
+            last_delta = exact_s[14];
+            status |= (uint32_t)exact_s[15];
+          } else {
+            last_delta = solve_and_compose(H, mu_m, mu_t, Rt, status);
+          }
           if (last_delta < a.min_delta) { status |= CCICP_ST_CONVERGED; break; }
         }
         if (!have_ok) status |= CCICP_ST_NO_CORR;

@@ -73,3 +73,12 @@ def test_c4_lockstep_first_iterations(ctx, oracle):
     corr, res = gpu_lockstep_corr(ctx, b.pair(0), tr["Rt_trace"][:-1])
     assert (corr == tr["corr"]).all(), "index mismatch in %d entries" % (corr != tr["corr"]).sum()
     assert (res["num_corr"] == tr["ncorr"]).all()
+
+
+def test_forced_l2_exact_sums_bit_identical(l2ctx, oracle):
+    b = scangen.generate(1000, 6)
+    prm = capi.fixed_iter_params(30, flags=capi.F_EXACT_SUMS)
+    res = l2ctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm)
+    for p in range(6):
+        r = oracle.fit(*b.pair(p), b.init_Rt()[p])
+        assert np.array_equal(np.r_[res[p]["R"], res[p]["t"]], r["Rt"])

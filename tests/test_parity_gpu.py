@@ -82,3 +82,36 @@ def test_c3_loop_closure_sample(ctx, oracle):
         r = oracle.fit(*b.pair(p), b.init_Rt()[p])
         assert_pose_close(np.r_[res[p]["R"], res[p]["t"]], r["Rt"], "C3 pair %d" % p)
         assert res[p]["num_corr"] == r["num_corr"]
+
+
+@pytest.mark.parametrize("seed,config,n", [(1, 1, 8), (1000, 1, 24), (10**6, 3, 16)])
+def test_exact_sums_mode_is_bit_identical(ctx, oracle, seed, config, n):
+    """CCICP_F_EXACT_SUMS: sequential-order sums + the reference's NR SVD -> R,t of a free-running 30-iteration fit
+    equal the reference's BIT FOR BIT (and with them every correspondence index of every iteration)."""
+    b = scangen.generate(seed, n, config=config)
+    prm = capi.fixed_iter_params(30, flags=capi.F_EXACT_SUMS)
+    res, corr = ctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm, want_corr=True)
+    for p in range(n):
+        tr = oracle.trace(*b.pair(p), b.init_Rt()[p], max_iter=30, min_delta=-2.0)
+        got = np.r_[res[p]["R"], res[p]["t"]]
+        assert np.array_equal(got.view(np.uint64), np.asarray(tr["Rt"], np.float64).view(np.uint64)), \
+            "pair %d: max |diff| %g" % (p, np.abs(got - tr["Rt"]).max())
+        assert res[p]["last_delta"] == tr["delta"][-1]
+        so = b.scene_off
+        assert (corr[0, so[2 * p]:so[2 * p + 2]] == tr["corr"][-1]).all()
+        assert res[p]["num_corr"] == tr["ncorr"][-1]
+
+
+def test_exact_sums_early_exit_and_lockstep(ctx, oracle):
+    """Default stop rule with exact sums: identical iteration count and identical final R,t; one exact fitStep from
+    every oracle R,t reproduces the next oracle R,t exactly."""
+    b = scangen.generate(40, 8, params=scangen.default_params(1, off_xy=0.05, off_th=0.01))
+    prm = capi.default_params(max_iter=200, flags=capi.F_EXACT_SUMS)
+    res = ctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm)
+    for p in range(8):
+        tr = oracle.trace(*b.pair(p), b.init_Rt()[p], max_iter=200, min_delta=1e-6)
+        assert res[p]["iters"] == tr["iters"]
+        assert np.array_equal(np.r_[res[p]["R"], res[p]["t"]], tr["Rt"])
+    tr = oracle.trace(*b.pair(0), b.init_Rt()[0], max_iter=12, min_delta=-2.0)
+    corr, r1 = gpu_lockstep_corr(ctx, b.pair(0), tr["Rt_trace"][:-1], flags=capi.F_EXACT_SUMS)
+    assert np.array_equal(np.c_[r1["R"], r1["t"]], tr["Rt_trace"][1:])
