@@ -70,7 +70,7 @@ enum {
   CCICP_F_NO_TIE_REPLAY  = 1u << 3, /* diagnostics only: skip the kd-tree tie replay (ties -> lowest grid slot)                 */
   CCICP_F_EXACT_SUMS     = 1u << 4  /* evaluate centroids, H, the SVD (Matrix::svd, matrix.cpp:582-810) and the compose step in
                                        the reference's own sequential order: R,t of every iteration are then BIT-IDENTICAL to
-                                       the reference (about 1.5x slower; default is a parallel sum + closed form, ~1e-13 m off) */
+                                       the reference (about 4x slower; default is a parallel sum + closed form, ~1e-13 m off)   */
 };
 
 typedef struct ccicp_params {

@@ -62,40 +62,64 @@ __device__ __forceinline__ double solve_and_compose(const double* H, const doubl
 }
 
 // CCICP_F_EXACT_SUMS: statistics and solve of one fitStep in the reference's evaluation order (exact_solve.cuh).
-// Lanes 0..3 of warp 0 carry the four independent sequential accumulators of each pass; lane 0 runs the SVD.
+// Warp 0 does it: per chunk of 32 scene points every lane prepares one pair (transform, model point) in parallel,
+// then the accepted pairs are fed IN ORDER to the accumulators by warp shuffles, so the only serial chain is the
+// FP64 add itself.  Lane L carries accumulator L & 3 (the other lanes hold redundant copies); lane 0 runs the SVD.
 // ex[0..3] = mu_m, mu_t; ex[4..7] = H; ex[8..13] = new R,t; ex[14] = delta; ex[15] = status bits.
+// Stages the accepted pairs of scene points [i0, i0+32) in order into buf[k][4] = {m.x, m.y, q.x, q.y} as doubles
+// (the float -> double widening is exact, :83-84); returns how many there are.
+__device__ __forceinline__ int exact_stage(const Smem& s, const double* Rt, int ns, int i, int lane, double* buf) {
+  bool valid = false;
+  float qx = 0.0f, qy = 0.0f;
+  float2 m = make_float2(0.0f, 0.0f);
+  if (i < ns) {
+    const unsigned slot = s.slots[i];
+    if (slot != kNoSlot) {
+      valid = true;
+      const double2 sp = s.scene[i];
+      transform(Rt, sp.x, sp.y, qx, qy);
+      m = s.mpts[slot];
+    }
+  }
+  const unsigned mask = __ballot_sync(0xffffffffu, valid);
+  if (valid) {
+    double* d = buf + 4 * __popc(mask & ((1u << lane) - 1u));
+    d[0] = (double)m.x; d[1] = (double)m.y; d[2] = (double)qx; d[3] = (double)qy;
+  }
+  __syncwarp();
+  return __popc(mask);
+}
+
 __device__ __noinline__ void exact_step(const Smem& s, const double* Rt, int ns, int n, int tid, double* ex) {
-  if (tid < 4) {
-    const int cm = tid & 1, ct = tid >> 1;
+  if (tid < 32) {
+    const int lane = tid, q4 = lane & 3;
+    double* buf = s.red;                                   // both parity buffers are idle here: 160 >= 128 doubles
     double acc = 0.0;
+    for (int i0 = 0; i0 < ns; i0 += 32) {                  // icpPointToPoint.cpp:80-86, 115-121 (scene order, GA first)
+      const int cnt = exact_stage(s, Rt, ns, i0 + lane, lane, buf);
 #pragma unroll 4
-    for (int i = 0; i < ns; i++) {                         // icpPointToPoint.cpp:80-86, 115-121 (scene order, GA first)
-      const unsigned slot = s.slots[i];
-      if (slot == kNoSlot) continue;
-      const double2 sp = s.scene[i];
-      float qx, qy;
-      transform(Rt, sp.x, sp.y, qx, qy);
-      const float2 m = s.mpts[slot];
-      const double v = tid < 2 ? (double)(cm ? m.y : m.x) : (double)(cm ? qy : qx);
-      acc += v;
+      for (int k = 0; k < cnt; k++) acc += buf[4 * k + q4];
+      __syncwarp();
     }
-    ex[tid] = acc / (double)n;                             // :149-150
-    __syncwarp(0xFu);
-    const double mu_m = ex[cm], mu_t = ex[2 + ct];
+    const double mu = acc / (double)n;                     // :149-150
+    const double mu_m0 = __shfl_sync(0xffffffffu, mu, 0), mu_m1 = __shfl_sync(0xffffffffu, mu, 1);
+    const double mu_t0 = __shfl_sync(0xffffffffu, mu, 2), mu_t1 = __shfl_sync(0xffffffffu, mu, 3);
+    if (lane < 4) ex[lane] = mu;
+    // H[ct][cm] = sum_k (p_t[k][ct] - mu_t[ct]) * (p_m[k][cm] - mu_m[cm]), lane = 2*ct + cm
+    const int cm = lane & 1, ct = (lane >> 1) & 1;
+    const double my_mu_m = cm ? mu_m1 : mu_m0, my_mu_t = ct ? mu_t1 : mu_t0;
     double h = 0.0;
+    for (int i0 = 0; i0 < ns; i0 += 32) {
+      const int cnt = exact_stage(s, Rt, ns, i0 + lane, lane, buf);
 #pragma unroll 4
-    for (int i = 0; i < ns; i++) {                         // H[ct][cm] = sum_k (p_t[k][ct]-mu_t[ct]) * (p_m[k][cm]-mu_m[cm])
-      const unsigned slot = s.slots[i];
-      if (slot == kNoSlot) continue;
-      const double2 sp = s.scene[i];
-      float qx, qy;
-      transform(Rt, sp.x, sp.y, qx, qy);
-      const float2 m = s.mpts[slot];
-      const double pt = (double)(ct ? qy : qx), pm = (double)(cm ? m.y : m.x);
-      h += __dmul_rn(pt - mu_t, pm - mu_m);
+      for (int k = 0; k < cnt; k++) {
+        const double pm = buf[4 * k + cm], pt = buf[4 * k + 2 + ct];
+        h += __dmul_rn(pt - my_mu_t, pm - my_mu_m);
+      }
+      __syncwarp();
     }
-    ex[4 + tid] = h;
-    __syncwarp(0xFu);
+    if (lane < 4) ex[4 + lane] = h;
+    __syncwarp();
     if (tid == 0) {
       const double H[4] = {ex[4], ex[5], ex[6], ex[7]};
       const double mu_m2[2] = {ex[0], ex[1]}, mu_t2[2] = {ex[2], ex[3]};
