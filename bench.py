@@ -188,6 +188,7 @@ def gpu_arm(args, rank, world, local_rank):
     alg_bytes = algorithmic_bytes(batch)
     prm = capi.fixed_iter_params(ITERS, indist=INDIST)
     ctx = capi.Context(local_rank)
+    cells_hint = capi.max_cells(batch.model_off)       # what the host-buffer call computes itself from the offsets
 
     # device-resident copies (the "value" leg starts with inputs in HBM)
     t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a).view(dt).reshape(-1)).to(dev)
@@ -200,7 +201,7 @@ def gpu_arm(args, rank, world, local_rank):
     def step_device():
         ctx.register_batch_device(n_pairs, 1, d_mxy.data_ptr(), d_moff.data_ptr(), d_sxy.data_ptr(), d_soff.data_ptr(),
                                   d_init.data_ptr(), prm, d_out.data_ptr(), 0, batch.max_model, batch.max_scene,
-                                  stream.cuda_stream)
+                                  stream.cuda_stream, max_cells_hint=cells_hint)
         if world > 1:      # the path's only exchange: gather the per-pair records
             return sharding.gather_records(d_out, world, n_pairs * world)
         return d_out

@@ -59,7 +59,9 @@ enum {
   CCICP_ST_CONVERGED     = 1u << 6, /* stopped because delta < min_delta (icp.cpp:119-120)                                     */
   CCICP_ST_TREE_OVERFLOW = 1u << 7, /* tie replay needed a deeper kd-tree than the replay stack supports; tie left to the
                                        grid's lowest-slot rule                                                                  */
-  CCICP_ST_INFO_SINGULAR = 1u << 8  /* getEdgeWeight's 3x3 system was singular / ss == 0; info[] holds inf/nan like the ref    */
+  CCICP_ST_INFO_SINGULAR = 1u << 8, /* getEdgeWeight's 3x3 system was singular / ss == 0; info[] holds inf/nan like the ref    */
+  CCICP_ST_HINT_TOO_SMALL = 1u << 9 /* max_cells_hint of ccicp_register_batch_device_ex was too small for this pair: not
+                                       registered, R,t returned unchanged                                                      */
 };
 
 /* ---- flags (ccicp_params.flags) ---------------------------------------- */
@@ -146,6 +148,17 @@ int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds
                                 const double* d_init_Rt, const ccicp_params* params,
                                 ccicp_result* d_out, int32_t* d_corr_idx,
                                 int32_t max_model, int32_t max_scene, void* stream);
+/* Same with a hint for the shared-memory cell table: max over the pairs of ccicp_grid_cells(nGA) + ccicp_grid_cells(nNGA)
+ * (model points per class).  0 = unknown: the worst case for max_model is assumed, which can cost one resident
+ * CTA per SM.  The hint is checked on the device: a pair that needs more cells is not registered and is reported
+ * with status CCICP_ST_HINT_TOO_SMALL (R,t unchanged).                                                          */
+int ccicp_register_batch_device_ex(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
+                                   const double* d_model_xy, const int32_t* d_model_off,
+                                   const double* d_scene_xy, const int32_t* d_scene_off,
+                                   const double* d_init_Rt, const ccicp_params* params,
+                                   ccicp_result* d_out, int32_t* d_corr_idx,
+                                   int32_t max_model, int32_t max_scene, int32_t max_cells_hint, void* stream);
+int32_t ccicp_grid_cells(int32_t n_class_points);   /* cells of the table for a class of n model points */
 int ccicp_stream_sync(ccicp_ctx* ctx, void* stream);
 
 /* ---- the immediate caller, batched: CCICP::doICPMatch(model_GA, model_NGA, scene_GA, scene_NGA, initPose)

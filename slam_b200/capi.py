@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("CCICP_LIB") or os.path.join(_HERE, "lib", "libccicp2d
 # error codes / status bits / flags (mirror the header)
 OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
 ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
-ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR = 32, 64, 128, 256
+ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
 F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS = 1, 2, 4, 8, 16
 
 
@@ -39,7 +39,8 @@ assert RESULT_DTYPE.itemsize == 160
 SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror", "ccicp_last_cuda_error",
            "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
            "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_rt",
-           "ccicp_rt_to_pose", "ccicp_classify_points", "ccicp_classify_points_device"]
+           "ccicp_rt_to_pose", "ccicp_classify_points", "ccicp_classify_points_device", "ccicp_register_batch_device_ex",
+           "ccicp_grid_cells"]
 
 _lib = None
 
@@ -70,6 +71,9 @@ def load():
     lib.ccicp_default_params.restype = None
     lib.ccicp_register_batch.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
     lib.ccicp_register_batch_device.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, vp]
+    lib.ccicp_register_batch_device_ex.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, i32, vp]
+    lib.ccicp_grid_cells.argtypes = [i32]
+    lib.ccicp_grid_cells.restype = i32
     lib.ccicp_stream_sync.argtypes = [vp, vp]
     lib.ccicp_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     lib.ccicp_host_free.argtypes = [vp]
@@ -188,11 +192,11 @@ class Context:
                                                           d_out_src or None, d_out_cnt, stream or None))
 
     def register_batch_device(self, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt,
-                              params, d_out, d_corr, max_model, max_scene, stream=None):
+                              params, d_out, d_corr, max_model, max_scene, stream=None, max_cells_hint=0):
         """Device-pointer call (ints from tensor.data_ptr()); asynchronous on `stream` (cudaStream_t as int)."""
-        rc = self.lib.ccicp_register_batch_device(self.h, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy,
-                                                  d_scene_off, d_init_Rt, C.byref(params), d_out, d_corr or None,
-                                                  max_model, max_scene, stream or None)
+        rc = self.lib.ccicp_register_batch_device_ex(self.h, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy,
+                                                     d_scene_off, d_init_Rt, C.byref(params), d_out, d_corr or None,
+                                                     max_model, max_scene, max_cells_hint, stream or None)
         self._check(rc)
 
     def sync(self, stream=None):
@@ -202,6 +206,16 @@ class Context:
         li = LaunchInfo()
         self._check(self.lib.ccicp_get_launch_info(self.h, C.byref(li)))
         return li
+
+
+def max_cells(model_off):
+    """max over pairs of ccicp_grid_cells(nGA) + ccicp_grid_cells(nNGA): the hint of register_batch_device."""
+    lib = load()
+    off = np.asarray(model_off, np.int64)
+    sizes = np.diff(off)
+    cells = {int(n): lib.ccicp_grid_cells(int(n)) for n in np.unique(sizes)}
+    per = np.array([cells[int(n)] for n in sizes], np.int64)
+    return int((per[0::2] + per[1::2]).max()) if len(per) else 0
 
 
 def pinned_array(shape, dtype):

@@ -268,11 +268,25 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   return CCICP_OK;
 }
 
+int32_t ccicp_grid_cells(int32_t n_class_points) {
+  const int g = grid_side(n_class_points);
+  return g * g;
+}
+
 int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy,
                                 const int32_t* d_model_off, const double* d_scene_xy, const int32_t* d_scene_off,
                                 const double* d_init_Rt, const ccicp_params* params, ccicp_result* d_out,
                                 int32_t* d_corr_idx, int32_t max_model, int32_t max_scene, void* stream) {
-  if (!ctx || !params || n_pairs < 0 || n_seeds < 1 || max_model < 0 || max_scene < 0) return CCICP_E_INVALID;
+  return ccicp_register_batch_device_ex(ctx, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt,
+                                        params, d_out, d_corr_idx, max_model, max_scene, 0, stream);
+}
+
+int ccicp_register_batch_device_ex(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy,
+                                   const int32_t* d_model_off, const double* d_scene_xy, const int32_t* d_scene_off,
+                                   const double* d_init_Rt, const ccicp_params* params, ccicp_result* d_out,
+                                   int32_t* d_corr_idx, int32_t max_model, int32_t max_scene, int32_t max_cells_hint,
+                                   void* stream) {
+  if (!ctx || !params || n_pairs < 0 || n_seeds < 1 || max_model < 0 || max_scene < 0 || max_cells_hint < 0) return CCICP_E_INVALID;
   if (n_pairs > 0 && (!d_model_xy || !d_model_off || !d_scene_xy || !d_scene_off || !d_init_Rt || !d_out)) return CCICP_E_INVALID;
   if (d_corr_idx && n_seeds > 1 && (params->flags & CCICP_F_BEST_OF_SEEDS)) return CCICP_E_INVALID;
   CK(cudaSetDevice(ctx->device));
@@ -286,7 +300,7 @@ int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds
   }
   ctx->timed_copies = false;
   return launch_icp(ctx, 0, 0, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt, params, d_out,
-                    d_corr_idx, max_model, max_scene, 0, total_scene, st);
+                    d_corr_idx, max_model, max_scene, max_cells_hint, total_scene, st);
 }
 
 int ccicp_stream_sync(ccicp_ctx* ctx, void* stream) {

@@ -178,8 +178,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
     const int s0 = a.scene_off[2 * pair], nsGA = a.scene_off[2 * pair + 1] - s0, nsNGA = a.scene_off[2 * pair + 2] - a.scene_off[2 * pair + 1];
     const int ns = nsGA + nsNGA;
     const bool model_ok = nmGA + nmNGA >= 5, scene_ok = ns >= 5;
+    // capacity of this launch's working set (a caller-supplied cell hint may be too small for this pair)
+    const bool fits = grid_side(nmGA) * grid_side(nmGA) + grid_side(nmNGA) * grid_side(nmNGA) <= a.ccap &&
+                      nmGA + nmNGA <= a.mcap && ns <= a.scap;
 
-    if (model_ok && scene_ok) {
+    if (model_ok && scene_ok && fits) {
       build_grid<kThreads>(a, s, m0, nmGA, nmNGA, tid);
       const double2* src = (const double2*)a.scene_xy + s0;
       if (kGlobal) {
@@ -208,6 +211,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
 
       if (!model_ok) status |= CCICP_ST_TOO_FEW_MODEL;
       else if (!scene_ok) status |= CCICP_ST_TOO_FEW_SCENE;
+      else if (!fits) status |= CCICP_ST_HINT_TOO_SMALL;
       else {
         const GridP& gp = s.grid[nmNGA >= nmGA];
         const double pcx = (double)gp.cx, pcy = (double)gp.cy;     // pivot of the shifted sums
