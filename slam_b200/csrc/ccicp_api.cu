@@ -23,10 +23,11 @@ struct ccicp_ctx {
   int sm_count = 0;
   int max_smem_optin = 0;
   cudaStream_t stream = nullptr;
-  cudaStream_t copy_stream = nullptr, kstream[2] = {nullptr, nullptr};   // chunked host path: H2D overlaps compute
+  cudaStream_t copy_stream = nullptr, kstream[4] = {nullptr, nullptr, nullptr, nullptr};   // chunked host path: H2D overlaps compute
   cudaEvent_t chunk_ev[16] = {};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
   bool timed = false, timed_copies = false;
+  int chunk_pairs = 384;      // CCICP_CHUNK_PAIRS: pairs per H2D/compute chunk of the host-buffer call
   int stage_kb = 200;         // CCICP_STAGE_KB
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the L2 variant
   void* timed_stream = nullptr;
@@ -90,8 +91,11 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   a.ccap = max_cells > 0 ? max_cells : max_cells_for(max_model);
   if (a.ccap < 64) a.ccap = 64;
   // on-chip variant when the pair's working set fits the SM's shared memory, else the L2 variant
+  const bool exact = (prm->flags & CCICP_F_EXACT_SUMS) != 0;
+  auto k_on = exact ? icp_pair_exact_kernel : icp_pair_kernel;
+  auto k_l2 = exact ? icp_pair_l2_exact_kernel : icp_pair_l2_kernel;
   cudaFuncAttributes fa_on;
-  CK(cudaFuncGetAttributes(&fa_on, icp_pair_kernel));
+  CK(cudaFuncGetAttributes(&fa_on, k_on));
   size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false);
   const bool use_l2 = smem + fa_on.sharedSizeBytes > (size_t)ctx->max_smem_optin || ctx->force_l2;
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
@@ -101,11 +105,11 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     // what is left of the SM's 256 KB stays L1 cache for the workspace
     a.stage_cap = (ctx->stage_kb * 1024 / 6) & ~31;
     smem = (size_t)a.stage_cap * 6;
-    CK(cudaFuncSetAttribute(icp_pair_l2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_l2_kernel, threads, smem));
+    CK(cudaFuncSetAttribute(k_l2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_l2, threads, smem));
   } else {
-    CK(cudaFuncSetAttribute(icp_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_kernel, threads, smem));
+    CK(cudaFuncSetAttribute(k_on, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_on, threads, smem));
   }
   if (occ < 1) return CCICP_E_TOO_LARGE;
   const int resident = occ * ctx->sm_count;
@@ -133,28 +137,26 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   if (rc) return rc;
   const size_t per_cta = replay_scratch_bytes(max_model);
   const size_t per_slot = per_cta * (size_t)resident;
-  if (slot == 0 || ctx->scratch.cap < per_slot * 2) {
-    if (ctx->scratch.cap < per_slot * 2) {
-      if (slot != 0) return CCICP_E_INVALID;      // sized by the first launch of a call
-      rc = reserve(ctx, ctx->scratch, per_slot * 2);
-      if (rc) return rc;
-    }
+  if (ctx->scratch.cap < per_slot * 4) {
+    if (slot != 0) return CCICP_E_INVALID;      // sized by the first launch of a call
+    rc = reserve(ctx, ctx->scratch, per_slot * 4);
+    if (rc) return rc;
   }
 
   if (use_l2) {
     a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true);
     const size_t ws_slot = a.workspace_per_cta * (size_t)resident;
-    if (ctx->workspace.cap < ws_slot * 2) {
+    if (ctx->workspace.cap < ws_slot * 4) {
       if (slot != 0) return CCICP_E_INVALID;
-      rc = reserve(ctx, ctx->workspace, ws_slot * 2);
+      rc = reserve(ctx, ctx->workspace, ws_slot * 4);
       if (rc) return rc;
     }
-    a.workspace = (char*)ctx->workspace.p + (size_t)(slot & 1) * ws_slot;
+    a.workspace = (char*)ctx->workspace.p + (size_t)(slot & 3) * ws_slot;
   }
   a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
   a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
   a.work_counter = (int32_t*)ctx->counter.p + (slot & 15);
-  a.scratch = (char*)ctx->scratch.p + (size_t)(slot & 1) * per_slot; a.scratch_per_cta = per_cta;
+  a.scratch = (char*)ctx->scratch.p + (size_t)(slot & 3) * per_slot; a.scratch_per_cta = per_cta;
   a.pair_base = pair_base;
   a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
   a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
@@ -162,8 +164,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
 
   CK(cudaMemsetAsync(a.work_counter, 0, 4, st));
   if (slot == 0) CK(cudaEventRecord(ctx->ev[2], st));
-  if (use_l2) icp_pair_l2_kernel<<<grid, threads, smem, st>>>(a);
-  else icp_pair_kernel<<<grid, threads, smem, st>>>(a);
+  if (use_l2) k_l2<<<grid, threads, smem, st>>>(a);
+  else k_on<<<grid, threads, smem, st>>>(a);
   CK(cudaGetLastError());
   ctx->info.n_launches += 1;
   if (best_of) {
@@ -176,7 +178,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   CK(cudaEventRecord(ctx->ev[3], st));
   ctx->timed = true; ctx->timed_stream = (void*)st;
   cudaFuncAttributes fa = fa_on;
-  if (use_l2) CK(cudaFuncGetAttributes(&fa, icp_pair_l2_kernel));
+  if (use_l2) CK(cudaFuncGetAttributes(&fa, k_l2));
   ctx->info.grid = grid; ctx->info.block = threads; ctx->info.smem_bytes = (int)(smem + fa.sharedSizeBytes);
   ctx->info.regs_per_thread = fa.numRegs; ctx->info.blocks_per_sm = occ; ctx->info.kernel_variant = use_l2 ? 1 : 0;
   ctx->info.sm_count = ctx->sm_count;
@@ -231,6 +233,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   if (!ctx) return CCICP_E_NOMEM;
   ctx->device = device;
   { const char* e = getenv("CCICP_FORCE_L2"); ctx->force_l2 = e && e[0] == '1'; }
+  { const char* e = getenv("CCICP_CHUNK_PAIRS"); if (e && atoi(e) >= 16) ctx->chunk_pairs = atoi(e); }
   { const char* e = getenv("CCICP_STAGE_KB"); if (e && atoi(e) >= 1 && atoi(e) <= 216) ctx->stage_kb = atoi(e); }
   cudaDeviceProp prop;
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
@@ -350,8 +353,8 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   // are absolute, so every chunk's kernel indexes the same device arrays with a different pair_base.
   int n_chunks = 1;
   if (n_seeds == 1 && !corr_idx) {
-    n_chunks = n_pairs / 1024;
-    if (n_chunks > 8) n_chunks = 8;
+    n_chunks = n_pairs / ctx->chunk_pairs;       // up to 4 chunk kernels are in flight (4 streams, 4 scratch slots)
+    if (n_chunks > 16) n_chunks = 16;
     if (n_chunks < 1) n_chunks = 1;
   }
   cudaStream_t cs = ctx->copy_stream;
@@ -368,7 +371,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
                        (size_t)(p1 - p0) * n_seeds * 48, cudaMemcpyHostToDevice, cs));
     CK(cudaEventRecord(ctx->chunk_ev[c], cs));
     if (c == n_chunks - 1) CK(cudaEventRecord(ctx->ev[1], cs));
-    cudaStream_t ks = n_chunks == 1 ? st : ctx->kstream[c & 1];
+    cudaStream_t ks = n_chunks == 1 ? st : ctx->kstream[c & 3];
     CK(cudaStreamWaitEvent(ks, ctx->chunk_ev[c], 0));
     rc = launch_icp(ctx, p0, c, p1 - p0, n_seeds, (const double*)ctx->d_model.p, (const int32_t*)ctx->d_moff.p,
                     (const double*)ctx->d_scene.p, (const int32_t*)ctx->d_soff.p, (const double*)ctx->d_init.p, params,
@@ -386,7 +389,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   }
   CK(cudaStreamSynchronize(cs));
   if (n_chunks == 1) CK(cudaStreamSynchronize(st));
-  else { CK(cudaStreamSynchronize(ctx->kstream[0])); CK(cudaStreamSynchronize(ctx->kstream[1])); }
+  else { for (auto& ks : ctx->kstream) CK(cudaStreamSynchronize(ks)); }
   ctx->timed_copies = true;
   return CCICP_OK;
 }

@@ -148,13 +148,13 @@ __device__ __noinline__ void exact_step(const Smem& s, const double* Rt, int ns,
   }
 }
 
-template <int kThreads, bool kGlobal>
+template <int kThreads, bool kGlobal, bool kExact>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
   __shared__ double red_s[2 * kWarps * kRedStride];
   __shared__ double rtprev_s[8 + (kGlobal ? kWarps * 4 : 0)];     // + float[kWarps][8] min/max scratch of the tie replay
-  __shared__ double exact_s[16];
+  __shared__ double exact_s[kExact ? 16 : 1];
   __shared__ GridP grid_s[2];
   __shared__ int misc_s[16];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
@@ -278,7 +278,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];
           }
           // ---- a8, a9
-          if (a.flags & CCICP_F_EXACT_SUMS) {
+          if constexpr (kExact) {
             __syncthreads();                  // slots of this iteration are final and visible
             exact_step(s, Rt, ns, n, tid, exact_s);
             __syncthreads();
@@ -400,12 +400,20 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
 }
 
 __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_kernel(const IcpArgs a) {
-  icp_pair_body<kThreadsOnChip, false>(a);
+  icp_pair_body<kThreadsOnChip, false, false>(a);
 }
 
 // Large scans (config C4): same algorithm, working set in the CTA's global workspace (L2/L1 resident).
 __global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_kernel(const IcpArgs a) {
-  icp_pair_body<kThreadsL2, true>(a);
+  icp_pair_body<kThreadsL2, true, false>(a);
+}
+
+// CCICP_F_EXACT_SUMS instantiations (separate kernels so the default ones carry none of their register pressure).
+__global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_exact_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsOnChip, false, true>(a);
+}
+__global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_exact_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsL2, true, true>(a);
 }
 
 // best-of-seeds: one warp per pair, arg-min of score over seeds with
