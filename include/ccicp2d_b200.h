@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CCICP_ABI_VERSION 1
+#define CCICP_ABI_VERSION 2
 
 /* ---- call-level error codes ------------------------------------------- */
 enum {
@@ -60,6 +60,8 @@ enum {
   CCICP_ST_TREE_OVERFLOW = 1u << 7, /* tie replay needed a deeper kd-tree than the replay stack supports; tie left to the
                                        grid's lowest-slot rule                                                                  */
   CCICP_ST_INFO_SINGULAR = 1u << 8, /* getEdgeWeight's 3x3 system was singular / ss == 0; info[] holds inf/nan like the ref    */
+  CCICP_ST_NO_SEED_BELOW = 1u << 10, /* CCICP_F_FIRST_BELOW: no seed reached score / n_scene < score_threshold; the record is the
+                                       arg-min seed instead (global_match.cpp:151-174 publishes nothing in that case)           */
   CCICP_ST_HINT_TOO_SMALL = 1u << 9 /* max_cells_hint of ccicp_register_batch_device_ex was too small for this pair: not
                                        registered, R,t returned unchanged                                                      */
 };
@@ -69,6 +71,9 @@ enum {
   CCICP_F_INFO           = 1u << 0, /* also compute the Lu-Milios information matrix (getEdgeWeight) into result.info         */
   CCICP_F_INFO_FIXED_DY  = 1u << 1, /* use dy = ay - by instead of the reference's dy = ax - bx (icpPointToPoint.cpp:262)      */
   CCICP_F_BEST_OF_SEEDS  = 1u << 2, /* n_seeds > 1: write one record per pair, the arg-min score seed (ties: lowest seed)       */
+  CCICP_F_FIRST_BELOW    = 1u << 5, /* with BEST_OF_SEEDS: global_matching's acceptance rule (global_match.cpp:131-151) -- the
+                                       FIRST seed (lowest index) whose normalised score  score / n_scene  is below
+                                       score_threshold wins, instead of the arg-min                                            */
   CCICP_F_NO_TIE_REPLAY  = 1u << 3, /* diagnostics only: skip the kd-tree tie replay (ties -> lowest grid slot)                 */
   CCICP_F_EXACT_SUMS     = 1u << 4  /* evaluate centroids, H, the SVD (Matrix::svd, matrix.cpp:582-810) and the compose step in
                                        the reference's own sequential order: R,t of every iteration are then BIT-IDENTICAL to
@@ -82,6 +87,8 @@ typedef struct ccicp_params {
   double   indist;     /* gate on the SQUARED float NN distance: keep iff (double)dis < indist
                           (icpPointToPoint.cpp:76,111); the facade passes 5 (icpTools.cpp:188)      */
   double   min_corr_frac; /* BEST_OF_SEEDS: a seed scores +inf unless num_corr >= frac * n_scene    */
+  double   score_threshold; /* FIRST_BELOW: accept a seed iff score / n_scene < threshold
+                               (MAX_SCORE 0.002, global_match.cpp:30)                               */
 } ccicp_params;
 
 /* One record per (pair, seed) problem -- 160 bytes. */

@@ -16,12 +16,13 @@ LIB_PATH = os.environ.get("CCICP_LIB") or os.path.join(_HERE, "lib", "libccicp2d
 OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
 ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
 ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
-F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS = 1, 2, 4, 8, 16
+ST_NO_SEED_BELOW = 1024
+F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW = 1, 2, 4, 8, 16, 32
 
 
 class Params(C.Structure):
     _fields_ = [("max_iter", C.c_int32), ("flags", C.c_uint32), ("min_delta", C.c_double),
-                ("indist", C.c_double), ("min_corr_frac", C.c_double)]
+                ("indist", C.c_double), ("min_corr_frac", C.c_double), ("score_threshold", C.c_double)]
 
 
 class LaunchInfo(C.Structure):

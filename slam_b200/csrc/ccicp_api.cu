@@ -171,7 +171,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   if (best_of) {
     const int threads = 128, warps_per_block = threads / 32;
     select_best_seed_kernel<<<(n_pairs + warps_per_block - 1) / warps_per_block, threads, 0, st>>>(
-        kernel_out, d_out, d_scene_off, n_pairs, n_seeds, prm->min_corr_frac);
+        kernel_out, d_out, d_scene_off + 2 * (size_t)pair_base, n_pairs, n_seeds, prm->min_corr_frac,
+        (prm->flags & CCICP_F_FIRST_BELOW) ? prm->score_threshold : -1.0);
     CK(cudaGetLastError());
     ctx->info.n_launches += 1;
   }
@@ -220,6 +221,7 @@ void ccicp_default_params(ccicp_params* p) {
   p->min_delta = 1e-6;       // icp.cpp:27
   p->indist = 5.0;           // icpTools.cpp:188
   p->min_corr_frac = 0.5;
+  p->score_threshold = 0.002;  // MAX_SCORE, global_match.cpp:30
 }
 
 int ccicp_create(ccicp_ctx** out, int device) {

@@ -416,36 +416,46 @@ __global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_exact_kernel(const 
   icp_pair_body<kThreadsL2, true, true>(a);
 }
 
-// best-of-seeds: one warp per pair, arg-min of score over seeds with
-// num_corr >= min_corr_frac * n_scene; ties -> lowest seed index.
+// best-of-seeds: one warp per pair.  Default: arg-min of score over seeds with num_corr >= min_corr_frac * n_scene,
+// ties -> lowest seed index.  first_below >= 0 (CCICP_F_FIRST_BELOW): the lowest seed index whose normalised score
+// score / n_scene is below the threshold (global_match.cpp:131-151); if there is none, the arg-min with
+// CCICP_ST_NO_SEED_BELOW.
 __global__ void select_best_seed_kernel(const ccicp_result* __restrict__ all, ccicp_result* __restrict__ out,
                                         const int32_t* __restrict__ scene_off, int n_pairs, int n_seeds,
-                                        double min_corr_frac) {
+                                        double min_corr_frac, double first_below) {
   const int pair = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (pair >= n_pairs) return;
-  const double need = min_corr_frac * (double)(scene_off[2 * pair + 2] - scene_off[2 * pair]);
+  const double n_scene = (double)(scene_off[2 * pair + 2] - scene_off[2 * pair]);
+  const double need = min_corr_frac * n_scene;
   double best = CUDART_INF;
-  int bseed = 0x7fffffff;
+  int bseed = 0x7fffffff, fseed = 0x7fffffff;
   for (int sd = lane; sd < n_seeds; sd += 32) {
     const ccicp_result& r = all[(size_t)pair * n_seeds + sd];
     double sc = ((double)r.num_corr >= need && r.num_corr > 0) ? r.score : CUDART_INF;
     if (sc < best) { best = sc; bseed = sd; }      // ascending sd per lane: first minimum kept
+    if (first_below >= 0.0 && sc / n_scene < first_below && sd < fseed) fseed = sd;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     double ob = __shfl_xor_sync(0xffffffffu, best, o);
     int os = __shfl_xor_sync(0xffffffffu, bseed, o);
     if (ob < best || (ob == best && os < bseed)) { best = ob; bseed = os; }
+    fseed = min(fseed, __shfl_xor_sync(0xffffffffu, fseed, o));
   }
   if (bseed == 0x7fffffff) bseed = 0;               // nothing qualified: report seed 0
-  const ccicp_result* src = &all[(size_t)pair * n_seeds + bseed];
+  const bool want_first = first_below >= 0.0;
+  const int pick = (want_first && fseed != 0x7fffffff) ? fseed : bseed;
+  const ccicp_result* src = &all[(size_t)pair * n_seeds + pick];
   ccicp_result* dst = &out[pair];
   const int4* s4 = (const int4*)src;
   int4* d4 = (int4*)dst;
   for (int q = lane; q < (int)(sizeof(ccicp_result) / 16); q += 32) d4[q] = s4[q];
   __syncwarp();
-  if (lane == 0 && !(best < CUDART_INF)) dst->score = CUDART_INF;
+  if (lane == 0) {
+    if (!(best < CUDART_INF) && pick == bseed) dst->score = CUDART_INF;
+    if (want_first && fseed == 0x7fffffff) dst->status |= CCICP_ST_NO_SEED_BELOW;
+  }
 }
 
 }  // namespace ccicp

@@ -144,3 +144,34 @@ def test_multi_seed_best_of(ctx, oracle):
         assert best[p]["best_seed"] == int(np.argmin(scores))
         k = best[p]["best_seed"]
         assert (best[p]["R"] == allr[p * n_seeds + k]["R"]).all() and best[p]["score"] == allr[p * n_seeds + k]["score"]
+
+
+def test_multi_seed_first_below_threshold(ctx):
+    """global_matching's acceptance rule (global_match.cpp:131-151) -- the FIRST seed whose
+    normalised score (score / n_scene) is below the threshold wins, not the arg-min; none below -> arg-min + flag."""
+    b = scangen.generate(2000, 6)
+    n_seeds = 16
+    hyp = np.stack([scangen.hypotheses(int(s), n_seeds) for s in b.seeds])
+    hyp[:, 1:, :2] *= 0.05
+    hyp[:, 1:, 2] = (hyp[:, 1:, 2] - np.pi) * 0.03
+    Rt0 = scangen.pose_to_Rt(hyp.reshape(-1, 3))
+    args = (b.model_xy, b.model_off, b.scene_xy, b.scene_off, Rt0)
+    allr = ctx.register_batch(*args, capi.fixed_iter_params(12), n_seeds=n_seeds).reshape(6, n_seeds)
+    ns = np.diff(b.scene_off)[0::2] + np.diff(b.scene_off)[1::2]
+    ok = allr["num_corr"] >= 0.5 * ns[:, None]
+    norm = np.where(ok, allr["score"], np.inf) / ns[:, None]
+    thr = float(np.median(norm[np.isfinite(norm)]))             # about half of the seeds pass
+    prm = capi.fixed_iter_params(12, flags=capi.F_BEST_OF_SEEDS | capi.F_FIRST_BELOW)
+    prm.score_threshold = thr
+    got = ctx.register_batch(*args, prm, n_seeds=n_seeds)
+    for p in range(6):
+        below = np.nonzero(norm[p] < thr)[0]
+        if len(below):
+            assert got[p]["best_seed"] == below[0] and not (got[p]["status"] & capi.ST_NO_SEED_BELOW)
+        else:
+            assert got[p]["best_seed"] == int(np.argmin(norm[p])) and (got[p]["status"] & capi.ST_NO_SEED_BELOW)
+        assert (got[p]["R"] == allr[p, got[p]["best_seed"]]["R"]).all()
+    prm.score_threshold = 1e-12                                  # nobody passes: arg-min + flag everywhere
+    got = ctx.register_batch(*args, prm, n_seeds=n_seeds)
+    assert ((got["status"] & capi.ST_NO_SEED_BELOW) != 0).all()
+    assert (got["best_seed"] == np.argmin(np.where(ok, allr["score"], np.inf), 1)).all()
