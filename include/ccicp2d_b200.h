@@ -62,6 +62,7 @@ enum {
   CCICP_ST_INFO_SINGULAR = 1u << 8, /* getEdgeWeight's 3x3 system was singular / ss == 0; info[] holds inf/nan like the ref    */
   CCICP_ST_NO_SEED_BELOW = 1u << 10, /* CCICP_F_FIRST_BELOW: no seed reached score / n_scene < score_threshold; the record is the
                                        arg-min seed instead (global_match.cpp:151-174 publishes nothing in that case)           */
+  CCICP_ST_EDGE_REJECTED = 1u << 11, /* ccicp_match_batch with reject_dist > 0: the result moved too far from the initial pose     */
   CCICP_ST_HINT_TOO_SMALL = 1u << 9 /* max_cells_hint of ccicp_register_batch_device_ex was too small for this pair: not
                                        registered, R,t returned unchanged                                                      */
 };
@@ -89,6 +90,11 @@ typedef struct ccicp_params {
   double   min_corr_frac; /* BEST_OF_SEEDS: a seed scores +inf unless num_corr >= frac * n_scene    */
   double   score_threshold; /* FIRST_BELOW: accept a seed iff score / n_scene < threshold
                                (MAX_SCORE 0.002, global_match.cpp:30)                               */
+  double   reject_dist;   /* ccicp_match_batch: > 0 enables graph_slam's bad-match test: status gets
+                             CCICP_ST_EDGE_REJECTED when |dx| or |dy| between initial and final pose exceeds this
+                             (DIST_MOVE_THRESH 10 m) ...                                            */
+  double   reject_rot;    /* ... or the wrapped |dyaw| exceeds this (ROT_MOVE_THRESH 0.2 rad)
+                             (graph_slam/src/graphSlamTools.cpp:332-362, graphSlamTools.h:35-36)    */
 } ccicp_params;
 
 /* One record per (pair, seed) problem -- 160 bytes. */
@@ -213,6 +219,26 @@ int ccicp_classify_points(ccicp_ctx* ctx, int32_t n_clouds, const float* xyz, co
 int ccicp_classify_points_device(ccicp_ctx* ctx, int32_t n_clouds, const float* d_xyz, const int32_t* d_cloud_off,
                                  int64_t n_points, float* d_out_xyz, uint8_t* d_out_ground_adj,
                                  int32_t* d_out_src_index, int32_t* d_out_count, void* stream);
+
+/* ---- the step after the path in graph_slam: 3-D Lu-Milios edge information ------------------------------
+ * computeEdgeInformationLUM(source_trans, target, max_corr_distance) (graph_slam/src/graphSlamTools.cpp:108-214;
+ * called with 0.75 at :302), SURVEY.md 8(f) rank 3, batched over edges.  source_xyz holds the source clouds ALREADY
+ * transformed by the registration result (as the reference expects), target_xyz the target clouds, float x,y,z;
+ * *_off are int32 [n_edges+1] in points.  info receives the 6x6 matrix row-major per edge (MM / s^2, or the identity
+ * when s^2 < 1e-13 / not finite: status[e] = 1), num_corr the number of point pairs closer than max_corr_distance.
+ * Nearest neighbours are exact in float squared distance (the reference uses PCL's KdTreeFLANN; ties -> lowest
+ * target index here).  Host buffers; synchronous.                                                              */
+int ccicp_edge_information_lum(ccicp_ctx* ctx, int32_t n_edges, const float* source_xyz, const int32_t* source_off,
+                               const float* target_xyz, const int32_t* target_off, double max_corr_distance,
+                               double* info, int32_t* num_corr, uint32_t* status);
+
+/* Loop-closure candidate generator of graph_slam: graphSlamGetKNN (graph_slam/src/graphSlamTools.cpp:72-106), host
+ * logic.  nodes_xy: [n_nodes][2] key-frame positions; the query node has index query_idx and position query_xy.
+ * Like the reference: only nodes 0 .. n_nodes-3 are considered, K is clipped to n_nodes-1, candidates are ordered by
+ * planar distance (ties: lower index first) and the query's own index is skipped.  Returns the number of candidate
+ * indices written to out (<= K).                                                                                  */
+int32_t ccicp_knn_candidates(const double* nodes_xy, int32_t n_nodes, const double* query_xy, int32_t query_idx,
+                             int32_t K, int32_t* out);
 
 /* Pinned host memory for callers that want the H2D/D2H copies to overlap. */
 int ccicp_host_alloc(void** out, size_t bytes);

@@ -67,6 +67,7 @@ def build_facade(force=False, verbose=False):
     if not os.path.exists(src):
         return None
     hdrs = [os.path.join(ROOT, "include", "ccicp2d", f) for f in os.listdir(os.path.join(ROOT, "include", "ccicp2d"))]
+    hdrs.append(os.path.join(ROOT, "include", "ccicp2d_b200.h"))       # struct layouts of the C ABI
     if force or _newer(out, [src] + hdrs):
         _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"), "-o", out, src,
               "-L" + LIB, "-lccicp2d_b200", "-Wl,-rpath,$ORIGIN"], verbose)
@@ -104,7 +105,7 @@ def build_callsite(force=False, verbose=False):
     # the batched doICPMatch facade (include/ccicp2d/icpToolsBatch.h) driven with Eigen/ROS-shaped stand-in types
     out2, src2 = os.path.join(d, "batch_demo_b200"), os.path.join(d, "batch_demo.cpp")
     hdr2 = os.path.join(ROOT, "include", "ccicp2d", "icpToolsBatch.h")
-    if force or _newer(out2, [src2, hdr2, os.path.join(LIB, "libccicp2d_b200.so")]):
+    if force or _newer(out2, [src2, hdr2, os.path.join(ROOT, "include", "ccicp2d_b200.h"), os.path.join(LIB, "libccicp2d_b200.so")]):
         _run(["g++", "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(ROOT, "include"), "-o", out2, src2, "-L" + LIB,
               "-lccicp2d_b200", "-Wl,-rpath,$ORIGIN/../../slam_b200/lib"], verbose)
     return out

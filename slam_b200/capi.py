@@ -16,13 +16,14 @@ LIB_PATH = os.environ.get("CCICP_LIB") or os.path.join(_HERE, "lib", "libccicp2d
 OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
 ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
 ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
-ST_NO_SEED_BELOW = 1024
+ST_NO_SEED_BELOW, ST_EDGE_REJECTED = 1024, 2048
 F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW = 1, 2, 4, 8, 16, 32
 
 
 class Params(C.Structure):
     _fields_ = [("max_iter", C.c_int32), ("flags", C.c_uint32), ("min_delta", C.c_double),
-                ("indist", C.c_double), ("min_corr_frac", C.c_double), ("score_threshold", C.c_double)]
+                ("indist", C.c_double), ("min_corr_frac", C.c_double), ("score_threshold", C.c_double),
+                ("reject_dist", C.c_double), ("reject_rot", C.c_double)]
 
 
 class LaunchInfo(C.Structure):
@@ -41,7 +42,7 @@ SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror
            "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
            "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_rt",
            "ccicp_rt_to_pose", "ccicp_classify_points", "ccicp_classify_points_device", "ccicp_register_batch_device_ex",
-           "ccicp_grid_cells"]
+           "ccicp_grid_cells", "ccicp_edge_information_lum", "ccicp_knn_candidates"]
 
 _lib = None
 
@@ -73,6 +74,9 @@ def load():
     lib.ccicp_register_batch.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
     lib.ccicp_register_batch_device.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, vp]
     lib.ccicp_register_batch_device_ex.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, i32, vp]
+    lib.ccicp_edge_information_lum.argtypes = [vp, i32, vp, vp, vp, vp, dbl, vp, vp, vp]
+    lib.ccicp_knn_candidates.argtypes = [vp, i32, vp, i32, i32, vp]
+    lib.ccicp_knn_candidates.restype = i32
     lib.ccicp_grid_cells.argtypes = [i32]
     lib.ccicp_grid_cells.restype = i32
     lib.ccicp_stream_sync.argtypes = [vp, vp]
@@ -172,6 +176,19 @@ class Context:
         self._check(rc)
         return (out, rec) if want_records else out
 
+    def edge_information_lum(self, source_clouds, target_clouds, max_corr_distance=0.75):
+        """Batched computeEdgeInformationLUM.  Lists of float32 [n,3] clouds (sources already transformed).
+        Returns (info [E,6,6], num_corr [E], status [E])."""
+        E = len(source_clouds)
+        cat = lambda cl: np.ascontiguousarray(np.concatenate([np.asarray(c, np.float32).reshape(-1, 3) for c in cl], 0)
+                                              if cl else np.zeros((0, 3), np.float32))
+        off = lambda cl: np.cumsum([0] + [len(c) for c in cl]).astype(np.int32)
+        s, t, so, to = cat(source_clouds), cat(target_clouds), off(source_clouds), off(target_clouds)
+        info = np.zeros((max(E, 1), 6, 6), np.float64); num = np.zeros(max(E, 1), np.int32); st = np.zeros(max(E, 1), np.uint32)
+        self._check(self.lib.ccicp_edge_information_lum(self.h, E, _ptr(s), _ptr(so), _ptr(t), _ptr(to), float(max_corr_distance),
+                                                        _ptr(info), _ptr(num), _ptr(st)))
+        return info[:E], num[:E], st[:E]
+
     def classify_points(self, xyz, cloud_off):
         """Batched CCICP::classifyPoints.  xyz float32 [N,3], cloud_off int32 [n_clouds+1].
         Returns a list of (xyz[k,3], ground_adj[k], src_index[k]) per cloud."""
@@ -207,6 +224,15 @@ class Context:
         li = LaunchInfo()
         self._check(self.lib.ccicp_get_launch_info(self.h, C.byref(li)))
         return li
+
+
+def knn_candidates(nodes_xy, query_xy, query_idx, K=3):
+    """graphSlamGetKNN: indices of the loop-closure candidates of a key frame (host logic)."""
+    nodes_xy = np.ascontiguousarray(nodes_xy, np.float64).reshape(-1, 2)
+    q = np.ascontiguousarray(query_xy, np.float64).reshape(2)
+    out = np.zeros(max(K, 1), np.int32)
+    n = load().ccicp_knn_candidates(_ptr(nodes_xy), len(nodes_xy), _ptr(q), int(query_idx), int(K), _ptr(out))
+    return out[:n].copy()
 
 
 def max_cells(model_off):

@@ -5,11 +5,14 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <algorithm>
+#include <cmath>
 #include <vector>
 
 #include "ccicp_pair_main.cuh"
 #include "pose_math.h"
 #include "classify.cuh"
+#include "lum.cuh"
 
 using namespace ccicp;
 
@@ -34,6 +37,7 @@ struct ccicp_ctx {
   DevBuf counter, scratch, all_results, workspace;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
   DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap;            // classification scratch
+  DevBuf l_src, l_soff, l_tgt, l_toff, l_dist, l_idx, l_info, l_num, l_status;   // Lu-Milios edge information
   DevBuf c_xyz, c_off, c_out_xyz, c_out_ga, c_out_src, c_out_cnt;             // classification, host-buffer path
   ccicp_launch_info info{};
   std::string last_err;
@@ -222,6 +226,8 @@ void ccicp_default_params(ccicp_params* p) {
   p->indist = 5.0;           // icpTools.cpp:188
   p->min_corr_frac = 0.5;
   p->score_threshold = 0.002;  // MAX_SCORE, global_match.cpp:30
+  p->reject_dist = 0.0;        // off; graph_slam uses 10 m / 0.2 rad (graphSlamTools.h:35-36)
+  p->reject_rot = 0.0;
 }
 
 int ccicp_create(ccicp_ctx** out, int device) {
@@ -262,7 +268,8 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
                     &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
-                    &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt};
+                    &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
+                    &ctx->l_dist, &ctx->l_idx, &ctx->l_info, &ctx->l_num, &ctx->l_status};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->chunk_ev) if (ev) cudaEventDestroy(ev);
@@ -427,8 +434,34 @@ int ccicp_match_batch(ccicp_ctx* ctx, int32_t n_pairs, const double* model_xy, c
     if (scene_off[2 * (size_t)p + 2] - scene_off[2 * (size_t)p] < 5) { ccicp_pose_math::sentinel(&out_pose[p]); continue; }
     const double Rt[6] = {rec[p].R[0], rec[p].R[1], rec[p].R[2], rec[p].R[3], rec[p].t[0], rec[p].t[1]};
     ccicp_pose_math::Rt_to_pose(Rt, init_pose[p], &out_pose[p]);
+    if (params->reject_dist > 0.0) {               // graphSlamTools.cpp:332-362
+      const double x_diff = std::fabs(init_pose[p].px - out_pose[p].px), y_diff = std::fabs(init_pose[p].py - out_pose[p].py);
+      double theta_diff = std::fabs(ccicp_pose_math::euler_ypr(init_pose[p].qx, init_pose[p].qy, init_pose[p].qz, init_pose[p].qw).yaw -
+                                    ccicp_pose_math::euler_ypr(out_pose[p].qx, out_pose[p].qy, out_pose[p].qz, out_pose[p].qw).yaw);
+      if (theta_diff > 2 * M_PI) theta_diff = theta_diff - 2 * M_PI;
+      else if (theta_diff > M_PI) theta_diff = 2 * M_PI - theta_diff;
+      if (x_diff > params->reject_dist || y_diff > params->reject_dist || theta_diff > params->reject_rot)
+        rec[p].status |= CCICP_ST_EDGE_REJECTED;
+    }
   }
   return CCICP_OK;
+}
+
+// graphSlamGetKNN (graphSlamTools.cpp:72-106)
+int32_t ccicp_knn_candidates(const double* nodes_xy, int32_t n_nodes, const double* query_xy, int32_t query_idx, int32_t K,
+                             int32_t* out) {
+  if (!nodes_xy || !query_xy || !out || n_nodes <= 0 || K <= 0) return 0;
+  K = std::min(n_nodes - 1, K);
+  std::vector<std::pair<double, int32_t>> sc;
+  for (int32_t i = 0; i < n_nodes - 2; i++) {
+    const double dx = nodes_xy[2 * i] - query_xy[0], dy = nodes_xy[2 * i + 1] - query_xy[1];
+    sc.emplace_back(std::sqrt(dx * dx + dy * dy), i);
+  }
+  std::stable_sort(sc.begin(), sc.end(), [](const std::pair<double, int32_t>& a, const std::pair<double, int32_t>& b) { return a.first < b.first; });
+  int32_t n = 0;
+  for (int32_t i = 0; i < K; i++)
+    if (i < (int32_t)sc.size() && query_idx != sc[i].second) out[n++] = sc[i].second;
+  return n;
 }
 
 // GA / NGA classification (CCICP::classifyPoints, icpTools.cpp:36-103), device buffers.
@@ -490,6 +523,54 @@ int ccicp_classify_points(ccicp_ctx* ctx, int32_t n_clouds, const float* xyz, co
     if (out_src_index) CK(cudaMemcpyAsync(out_src_index, ctx->c_out_src.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
   }
   CK(cudaMemcpyAsync(out_count, ctx->c_out_cnt.p, (size_t)n_clouds * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return CCICP_OK;
+}
+
+// 3-D Lu-Milios edge information (computeEdgeInformationLUM, graphSlamTools.cpp:108-214), one CTA per edge.
+int ccicp_edge_information_lum(ccicp_ctx* ctx, int32_t n_edges, const float* source_xyz, const int32_t* source_off,
+                               const float* target_xyz, const int32_t* target_off, double max_corr_distance, double* info,
+                               int32_t* num_corr, uint32_t* status) {
+  if (!ctx || n_edges < 0) return CCICP_E_INVALID;
+  if (n_edges == 0) return CCICP_OK;
+  if (!source_off || !target_off || !info || !num_corr || !status || source_off[0] != 0 || target_off[0] != 0) return CCICP_E_INVALID;
+  for (int32_t e = 0; e < n_edges; e++)
+    if (source_off[e + 1] < source_off[e] || target_off[e + 1] < target_off[e]) return CCICP_E_INVALID;
+  const size_t ns = (size_t)source_off[n_edges], nt = (size_t)target_off[n_edges];
+  if ((ns && !source_xyz) || (nt && !target_xyz)) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t offb = ((size_t)n_edges + 1) * 4;
+  if ((rc = reserve(ctx, ctx->l_src, ns * 12 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->l_tgt, nt * 12 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->l_soff, offb))) return rc;
+  if ((rc = reserve(ctx, ctx->l_toff, offb))) return rc;
+  if ((rc = reserve(ctx, ctx->l_dist, ns * 4 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->l_idx, ns * 4 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->l_info, (size_t)n_edges * 36 * 8))) return rc;
+  if ((rc = reserve(ctx, ctx->l_num, (size_t)n_edges * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->l_status, (size_t)n_edges * 4))) return rc;
+  if (ns) CK(cudaMemcpyAsync(ctx->l_src.p, source_xyz, ns * 12, cudaMemcpyHostToDevice, st));
+  if (nt) CK(cudaMemcpyAsync(ctx->l_tgt.p, target_xyz, nt * 12, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->l_soff.p, source_off, offb, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->l_toff.p, target_off, offb, cudaMemcpyHostToDevice, st));
+  lum::Args a{};
+  a.source_xyz = (const float*)ctx->l_src.p; a.source_off = (const int32_t*)ctx->l_soff.p;
+  a.target_xyz = (const float*)ctx->l_tgt.p; a.target_off = (const int32_t*)ctx->l_toff.p;
+  a.nn_dist = (float*)ctx->l_dist.p; a.nn_idx = (int32_t*)ctx->l_idx.p;
+  a.info = (double*)ctx->l_info.p; a.num_corr = (int32_t*)ctx->l_num.p; a.status = (uint32_t*)ctx->l_status.p;
+  a.max_corr_distance = max_corr_distance; a.n_edges = n_edges;
+  const int grid = n_edges < ctx->sm_count * 4 ? n_edges : ctx->sm_count * 4;
+  CK(cudaEventRecord(ctx->ev[2], st));
+  lum::lum_edge_kernel<<<grid, lum::kThreads, 0, st>>>(a);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(ctx->ev[3], st));
+  ctx->timed = true; ctx->timed_copies = false; ctx->timed_stream = (void*)st;
+  ctx->info.n_launches = 1; ctx->info.grid = grid; ctx->info.block = lum::kThreads; ctx->info.kernel_variant = 3;
+  CK(cudaMemcpyAsync(info, ctx->l_info.p, (size_t)n_edges * 36 * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(num_corr, ctx->l_num.p, (size_t)n_edges * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(status, ctx->l_status.p, (size_t)n_edges * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return CCICP_OK;
 }

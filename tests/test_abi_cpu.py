@@ -30,7 +30,7 @@ def test_every_declared_symbol_is_exported():
 def test_struct_layouts():
     assert capi.RESULT_DTYPE.itemsize == 160
     assert capi.RESULT_DTYPE.fields["info"][1] == 48 and capi.RESULT_DTYPE.fields["num_corr"][1] == 136
-    assert C.sizeof(capi.Params) == 40
+    assert C.sizeof(capi.Params) == 56
     p = capi.default_params()
     assert (p.max_iter, p.min_delta, p.indist, p.flags) == (20, 1e-6, 5.0, 0)      # icp.cpp:27, icpTools.cpp:188
 
@@ -61,3 +61,13 @@ def test_facade_library_exports_reference_class_surface():
     for want in ["Icp::Icp(double*, double*, int, int, int)", "Icp::fit(double*, double*, int, int, Matrix&, Matrix&, double, double)",
                  "Icp::getEdgeWeight(double*)", "Icp::getNumberCorrespondences()"]:
         assert want in syms, want
+
+
+def test_knn_candidates_follow_graph_slam_rules():
+    """graphSlamGetKNN (graphSlamTools.cpp:72-106): last two nodes never considered, K clipped, self skipped."""
+    xy = np.array([[0, 0], [1, 0], [2, 0], [3, 0], [10, 0], [0.5, 0]], float)
+    q = capi.knn_candidates(xy, xy[5], 5, K=3)
+    assert q.tolist() == [0, 1, 2]                      # nodes 4 and 5 are outside the i < n-2 loop; ties 0/1 -> lower index
+    assert capi.knn_candidates(xy, xy[1], 1, K=3).tolist() == [0, 2]          # itself is skipped but still uses a slot
+    assert capi.knn_candidates(xy[:3], xy[2], 2, K=3).tolist() == [0]        # K clipped to n-1 = 2, only node 0 in range
+    assert capi.knn_candidates(xy[:2], xy[1], 1, K=3).tolist() == []

@@ -86,3 +86,21 @@ def test_cpp_batch_facade(tmp_path, oracle, mode):
     got = np.array([ln.split() for ln in r.stdout.strip().splitlines()], float)
     want = np.stack([tf_port.do_icp_match(oracle, b.pair(p), poses[p]) for p in range(b.n_pairs)])
     _check(got[:, :7], want, "C++ facade " + mode)
+
+
+def test_match_batch_edge_rejection_rule(ctx, oracle):
+    """graph_slam's bad-match test (graphSlamTools.cpp:332-362) on the batched caller: flag iff the result moved more
+    than reject_dist in x or y or more than reject_rot in (wrapped) yaw away from the initial pose."""
+    from oracle import lum_port
+    rng = np.random.default_rng(8)
+    b = scangen.generate(500, 12, config=3)
+    poses = _init_poses(b, rng)
+    prm = capi.default_params()
+    prm.reject_dist, prm.reject_rot = 0.3, 0.06                       # tight, so that some of the 12 pairs trip it
+    out, rec = ctx.match_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, poses, prm, want_records=True)
+    flags = []
+    for p in range(b.n_pairs):
+        yaw0, yaw1 = tf_port.euler_ypr(poses[p, 3:])[0], tf_port.euler_ypr(out[p, 3:])[0]
+        flags.append(lum_port.edge_is_rejected((poses[p, 0], poses[p, 1], yaw0), (out[p, 0], out[p, 1], yaw1), 0.3, 0.06))
+    got = (rec["status"] & capi.ST_EDGE_REJECTED) != 0
+    assert got.tolist() == flags and 0 < sum(flags) < b.n_pairs
