@@ -56,9 +56,32 @@ def main():
         init = np.concatenate([scangen.pose_to_Rt(scangen.hypotheses(int(s), S)) for s in b.seeds], 0)
         prm5 = capi.fixed_iter_params(30, flags=capi.F_BEST_OF_SEEDS)
         run(ctx, "C5 256 seeds best-of", b, prm5, n_seeds=S, init=init, reps=2)
+    if "lum" in which:
+        bench_lum(ctx, pairs or 592)
     if "classify" in which:
         bench_classify(ctx, pairs or 256)
     ctx.close()
+
+
+def bench_lum(ctx, n_edges, pts=3000):
+    """batched computeEdgeInformationLUM; FP32-issue bound (n x m exact distance sweep)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_lum_gpu import cloud_pair
+    from oracle import lum_port
+    base = [cloud_pair(k, pts) for k in range(4)]
+    src = [base[k % 4][0] for k in range(n_edges)]; tgt = [base[k % 4][1] for k in range(n_edges)]
+    ms = []
+    for _ in range(4):
+        info, num, st = ctx.edge_information_lum(src, tgt, 0.75)
+        ms.append(ctx.launch_info().last_kernel_ms)
+    k = float(np.min(ms[1:]))
+    evals = sum(len(a) * len(b) for a, b in zip(src, tgt))
+    t0 = time.perf_counter(); lum_port.edge_information(base[0][0][:600], base[0][1], 0.75); cpu = time.perf_counter() - t0
+    print(json.dumps({"config": "computeEdgeInformationLUM", "edges": n_edges, "points_per_cloud": pts, "kernel_ms": k,
+                      "edges_per_s": n_edges / (k * 1e-3), "distance_evals_per_s": evals / (k * 1e-3),
+                      "fp32_ops_per_s": 8 * evals / (k * 1e-3), "fp32_unfused_peak_ops_per_s": 148 * 128 * 1.965e9,
+                      "frac_of_fp32_issue_peak": 8 * evals / (k * 1e-3) / (148 * 128 * 1.965e9),
+                      "cpu_port_edges_per_s_est": 1.0 / (cpu * len(base[0][0]) / 600.0), "mean_num_corr": float(num.mean())}), flush=True)
 
 
 def bench_classify(ctx, n_clouds, pts=70000):
