@@ -30,10 +30,13 @@ namespace ccicp {
 
 // Two instantiations of the same pair kernel (template <kThreads, kGlobal>):
 //   on-chip : 256 threads, the pair's working set in dynamic shared memory (scans up to ~6000 points per cloud)
-//   L2      : 768 threads, one CTA per SM, the working set in a per-CTA global workspace that stays L2/L1-resident
+//   L2      : 1024 threads (64 registers), one CTA per SM, the working set in a per-CTA global workspace that stays L2/L1-resident
 //             (scans up to CCICP_MAX_POINTS; config C4 = 32768 points per cloud)
 constexpr int kThreadsOnChip = 256;
-constexpr int kThreadsL2 = 768;
+#ifndef CCICP_L2_THREADS
+#define CCICP_L2_THREADS 1024
+#endif
+constexpr int kThreadsL2 = CCICP_L2_THREADS;
 constexpr int kRedStride = 10;     // doubles per warp in the reduction scratch (8 sums + 2 ints)
 constexpr unsigned kNoSlot = 0xFFFFu;
 
