@@ -239,6 +239,7 @@ def gpu_arm(args, rank, world, local_rank):
             ctx.register_batch(batch.model_xy, batch.model_off, batch.scene_xy, batch.scene_off, init_h, prm, out=out_h)
         torch.cuda.synchronize()
         e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        e2e_launches = int(ctx.launch_info().n_launches)      # chunk kernels of one host-buffer call
         barrier()
     clocks = sampler.stop() if rank == 0 else None
 
@@ -275,7 +276,9 @@ def gpu_arm(args, rank, world, local_rank):
         "e2e": {"value": world * n_pairs / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                 "d2h_bytes_per_step": d2h * world, "ms_per_step": e2e_ms,
                 "api": "ccicp_register_batch (C ABI, pinned host buffers)"},
-        "gpu_launches": int(li.n_launches) * args.steps * world,
+        # kernels of this library launched inside the two timed regions (device leg + host-buffer leg), all ranks
+        "gpu_launches": (int(li.n_launches) + e2e_launches) * args.steps * world,
+        "gpu_launches_detail": {"device_leg_per_step": int(li.n_launches), "e2e_leg_per_step": e2e_launches},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic.get("dram_bytes_per_launch") if traffic else None,
                      "kernel": "icp_pair_kernel", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,

@@ -37,6 +37,10 @@ constexpr int kThreadsOnChip = 256;
 #define CCICP_L2_THREADS 1024
 #endif
 constexpr int kThreadsL2 = CCICP_L2_THREADS;
+#ifndef CCICP_CAND_UNROLL
+#define CCICP_CAND_UNROLL 2
+#endif
+constexpr int kCandUnroll = CCICP_CAND_UNROLL;   // candidate loop of nn_search
 constexpr int kRedStride = 10;     // doubles per warp in the reduction scratch (8 sums + 2 ints)
 constexpr unsigned kNoSlot = 0xFFFFu;
 
@@ -250,7 +254,22 @@ __device__ __forceinline__ void nn_search(const float2* mpts, const uint16_t* cs
         if (y + 2 <= yb) { j2 = r0[2 * G + xs]; e2 = r0[2 * G + xe + 1]; }
         const int n0 = e0 - j0, n01 = n0 + (e1 - j1), tot = n01 + (e2 - j2);
         const int o1 = j1 - n0, o2 = j2 - n01;
-#pragma unroll 2
+#if CCICP_TWO_RANGE
+        if (n01 == tot) {                     // at most two rows hold candidates: one select less per candidate
+#pragma unroll kCandUnroll
+          for (int t = 0; t < tot; t++) {
+            const int j = t + (t < n0 ? j0 : o1);
+            const float2 p = mpts[j];
+            const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+            const float d = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+            bslot = d < best ? j : bslot;
+            second = fminf(second, fmaxf(d, best));
+            best = fminf(best, d);
+          }
+          continue;
+        }
+#endif
+#pragma unroll kCandUnroll
         for (int t = 0; t < tot; t++) {
           int off = o2;
           off = t < n01 ? o1 : off;
