@@ -72,7 +72,7 @@ struct IcpArgs {
 // cells per side for a class of n model points (0 = class never searched,
 // icpPointToPoint.cpp:59,93 skip a class whose model has <= 3 points)
 #ifndef CCICP_GHUGE
-#define CCICP_GHUGE 512    // cells per side for classes with > 8192 model points (L2 variant only; 256: -9 %, 1024: -4 % on C4)
+#define CCICP_GHUGE 1024   // cells per side for classes with > 8192 model points (L2 variant only; C4 wave: 256 -> 30.2, 512 -> 25.4, 1024 -> 23.7 ms)
 #endif
 __host__ __device__ inline int grid_side(int n) {
   if (n <= 3) return 0;

@@ -6,7 +6,70 @@ namespace ccicp {
 
 // ---- grid build: counting (single-digit radix) sort of the model on cell id -
 // a1 (icp.cpp:51-60): model doubles are rounded to float once, here.
+// In-place exclusive scan of n_ent uint16 counters in GLOBAL memory (L2 variant: up to 2 x 1024^2 cells).  Every warp
+// owns a contiguous region and walks it in 256-entry steps, each lane loading 8 consecutive counters as one 16-byte
+// vector, so both passes are fully coalesced (a thread-contiguous chunk per thread touches one 32-byte sector per
+// 2-byte counter and made the 512^2 table cost 2.3 ms per pair).
 template <int kThreads>
+__device__ __forceinline__ void scan_cells_global(uint16_t* a, int n_ent, uint32_t* wtot, int tid) {
+  constexpr int kWarps = kThreads / 32;
+  const int w = tid >> 5, lane = tid & 31;
+  const int per_warp = (((n_ent + kWarps - 1) / kWarps) + 255) & ~255;
+  const int beg = min(w * per_warp, n_ent), end = min(beg + per_warp, n_ent);
+  uint32_t total = 0;
+  for (int base = beg; base < end; base += 256) {
+    const int i0 = base + lane * 8;
+    uint32_t sum = 0;
+    if (i0 + 8 <= end) {
+      const uint4 v = *(const uint4*)(a + i0);
+      sum = (v.x & 0xffffu) + (v.x >> 16) + (v.y & 0xffffu) + (v.y >> 16) + (v.z & 0xffffu) + (v.z >> 16) + (v.w & 0xffffu) + (v.w >> 16);
+    } else {
+      for (int k = 0; k < 8; k++) if (i0 + k < end) sum += a[i0 + k];
+    }
+    total += sum;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+  __syncthreads();
+  if (lane == 0) wtot[w] = total;
+  __syncthreads();
+  uint32_t carry = 0;
+  for (int k = 0; k < w; k++) carry += wtot[k];
+  for (int base = beg; base < end; base += 256) {
+    const int i0 = base + lane * 8;
+    uint32_t c[8];
+    const bool vec = i0 + 8 <= end;
+    if (vec) {
+      const uint4 v = *(const uint4*)(a + i0);
+      c[0] = v.x & 0xffffu; c[1] = v.x >> 16; c[2] = v.y & 0xffffu; c[3] = v.y >> 16;
+      c[4] = v.z & 0xffffu; c[5] = v.z >> 16; c[6] = v.w & 0xffffu; c[7] = v.w >> 16;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; k++) c[k] = (i0 + k < end) ? a[i0 + k] : 0u;
+    }
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) sum += c[k];
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    uint32_t run = carry + incl - sum;
+    carry += __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t o8[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { o8[k] = run & 0xffffu; run += c[k]; }
+    if (vec) {
+      uint4 v;
+      v.x = o8[0] | (o8[1] << 16); v.y = o8[2] | (o8[3] << 16); v.z = o8[4] | (o8[5] << 16); v.w = o8[6] | (o8[7] << 16);
+      *(uint4*)(a + i0) = v;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; k++) if (i0 + k < end) a[i0 + k] = (uint16_t)o8[k];
+    }
+  }
+}
+
+template <int kThreads, bool kGlobal>
 __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int m0, int nGA, int nNGA, int tid) {
   constexpr int kWarps = kThreads / 32;
   const int nm = nGA + nNGA;
@@ -81,7 +144,9 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
   __syncthreads();
 
   // exclusive scan of the ncell+1 counters, in place
-  {
+  if (kGlobal) {
+    scan_cells_global<kThreads>(s.cstart, ncell + 1, (uint32_t*)s.red, tid);
+  } else {
     const int n_ent = ncell + 1;
     const int ch = (n_ent + kThreads - 1) / kThreads;
     const int beg = min(tid * ch, n_ent), end = min(beg + ch, n_ent);

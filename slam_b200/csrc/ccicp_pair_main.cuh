@@ -183,7 +183,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
                       nmGA + nmNGA <= a.mcap && ns <= a.scap;
 
     if (model_ok && scene_ok && fits) {
-      build_grid<kThreads>(a, s, m0, nmGA, nmNGA, tid);
+      build_grid<kThreads, kGlobal>(a, s, m0, nmGA, nmNGA, tid);
       const double2* src = (const double2*)a.scene_xy + s0;
       if (kGlobal) {
         s.scene = src;             // read the (L2-resident) input in place every iteration
