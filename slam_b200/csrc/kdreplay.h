@@ -451,6 +451,34 @@ KD_FN int lazy_init_coop(const P& pts, int n, I* ind, LNode* nodes, int* n_nodes
   return OK;
 }
 
+// The reference's in-place partition (select_on_coordinate_value, kdtree.cpp:294-317)
+//     lb = l, ub = u;  while (lb < ub) { if (v[lb] <= alpha) lb++; else { swap(lb, ub); ub--; } }
+// examines every element exactly once, in an order that only depends on the outcomes: after an element that stays
+// (<= alpha) the next one examined is the next untouched element from the FRONT, after one that is moved away the
+// next is the next untouched element from the BACK (the one just swapped in).  Kept elements end up at the front in
+// examination order, moved ones at the back in examination order from the right end, and the split index is
+// (#kept - 1).  That is what this branch-free formulation writes (both streams are pre-loaded, so the serial chain is
+// compare -> select instead of load -> compare -> branch -> swap).  In place: a front slot is written only after its
+// element was consumed, a back slot in the same step its element is consumed (already held in a register).
+KD_HD int partition_stream(float* v, uint16_t* ix, int n, float alpha) {
+  if (n <= 0) return -1;
+  int f = 1, bk = n - 1;                 // next untouched element of the front / back stream
+  int gl = 0, br = n - 1;                // next write slot for kept / moved elements
+  float cv = v[0]; uint16_t ci = ix[0];
+  float fv = n > 1 ? v[1] : 0.0f; uint16_t fi = n > 1 ? ix[1] : (uint16_t)0;
+  float bv = v[n - 1]; uint16_t bi = ix[n - 1];
+  for (int t = 0; t < n; t++) {
+    const bool keep = cv <= alpha;
+    const int dst = keep ? gl : br;
+    v[dst] = cv; ix[dst] = ci;
+    gl += keep ? 1 : 0; br -= keep ? 0 : 1;
+    cv = keep ? fv : bv; ci = keep ? fi : bi;
+    if (keep) { f++; if (f < n) { fv = v[f]; fi = ix[f]; } }
+    else { bk--; if (bk >= 0) { bv = v[bk]; bi = ix[bk]; } }
+  }
+  return gl - 1;
+}
+
 // Splits node `id` (uniform call).  Ranges larger than the staging capacity fall back to the sequential split
 // on thread 0.
 template <class P, class I, class C>
@@ -483,17 +511,7 @@ KD_FN int lazy_split_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int
     float sum = 0.0f;
     for (int k = 0; k < n; k++) sum += sv[k];
     const float average = sum / (float)n;
-    int lb = 0, ub = n - 1;
-    while (lb < ub) {
-      if (sv[lb] <= average) {
-        lb++;
-      } else {
-        const uint16_t ti = si[lb]; si[lb] = si[ub]; si[ub] = ti;
-        const float tv = sv[lb]; sv[lb] = sv[ub]; sv[ub] = tv;
-        ub--;
-      }
-    }
-    *co.bcast = (sv[lb] <= average) ? lb : lb - 1;
+    *co.bcast = partition_stream(sv, si, n, average);
   }
   co.sync();
   const int m = *co.bcast;                                  // last index (staged numbering) of the left child
