@@ -1,0 +1,266 @@
+// seg_sort.cuh -- hand-written stable SEGMENTED LSD radix sort of (uint32 key, uint32 value) pairs for sm_100a.
+//
+// Used by the GA / NGA classification (classify.cuh): the points of every cloud are ordered by bin while points of
+// one bin keep their input order -- exactly the order the reference builds with one std::vector per bin
+// (ccicp2d/src/icpTools.cpp:39-60).  The clouds are already contiguous in the input, so the cloud id is not part
+// of the key: every tile of 4096 elements belongs to one segment, and the digit histogram table is laid out
+// (segment, digit, tile-in-segment) so that ONE exclusive scan over the whole table yields global positions.
+// 7 bits per pass (three passes for the 21-bit bin index).  Per pass:
+//   seg_hist     per-tile digit histogram                       (pass 0: produced by the caller's key kernel)
+//   scan_*       exclusive scan of the table (chunk totals, scan of totals, per-chunk scan)
+//   seg_scatter  ranks the tile's elements (match_any inside a warp + per-warp digit counters, warp w owns the
+//                w-th contiguous 512 elements so the counters need no block barrier between rounds), sorts the tile
+//                in shared memory and writes runs of equal digits to consecutive addresses.  The last pass hands
+//                (position, key, value) to a functor instead of storing the pair: the consumer is fused in.
+// HBM traffic per element: pass 0: 4 B in (values are implicit) + 8 B out; later passes 4 B (hist) + 8 B + 8 B.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ssort {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kItems = 16;                      // elements per thread per tile
+constexpr int kTile = kThreads * kItems;        // 4096 elements per CTA
+constexpr int kWarpSpan = kTile / kWarps;       // 512 consecutive elements per warp
+constexpr int kBits = 7;
+constexpr int kDigits = 1 << kBits;
+
+struct Plan {                // device arrays, filled by plan_kernel / plan_fill_kernel
+  int32_t* tile_base;        // [n_seg + 1] first tile of each segment; tile_base[n_seg] = number of tiles
+  int32_t* tile_seg;         // [max_tiles] segment of each tile
+  int32_t n_seg;
+};
+
+// sum over segments of ceil(n_s / kTile) <= n / kTile + n_seg
+__host__ __device__ inline int max_tiles(int64_t n, int n_seg) { return (int)(n / kTile) + n_seg; }
+constexpr int kScanChunk = 1024 * 8;            // table entries per scan CTA: 1024 threads x 8
+__host__ __device__ inline size_t hist_words(int64_t n, int n_seg) {
+  const size_t m = (size_t)kDigits * max_tiles(n, n_seg);
+  return m + (m + kScanChunk - 1) / kScanChunk + 16;
+}
+__device__ __forceinline__ size_t hist_index(int tb, int tc, int t, int d) {
+  return (size_t)kDigits * tb + (size_t)d * tc + t;
+}
+
+__device__ __forceinline__ uint32_t block_excl_scan_1024(uint32_t sum, uint32_t* wsum, uint32_t& total) {
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  uint32_t incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  __syncthreads();
+  if (lane == 31) wsum[w] = incl;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t x = wsum[lane], xi = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, xi, o); if (lane >= o) xi += t; }
+    wsum[lane] = xi - x;                                   // exclusive offset of warp `lane`
+    if (lane == 31) wsum[32] = xi;                         // block total
+  }
+  __syncthreads();
+  total = wsum[32];
+  return wsum[w] + incl - sum;
+}
+
+// ---- tiling plan: one CTA scans the per-segment tile counts, a second kernel labels the tiles
+__global__ void __launch_bounds__(1024) plan_kernel(const int32_t* __restrict__ off, Plan p) {
+  __shared__ uint32_t wsum[33];
+  uint32_t carry = 0;
+  for (int base = 0; base < p.n_seg; base += 1024) {
+    const int s = base + threadIdx.x;
+    const uint32_t t = s < p.n_seg ? (uint32_t)((off[s + 1] - off[s] + kTile - 1) / kTile) : 0u;
+    uint32_t total;
+    const uint32_t ex = block_excl_scan_1024(t, wsum, total);
+    if (s < p.n_seg) p.tile_base[s] = (int32_t)(carry + ex);
+    carry += total;
+  }
+  if (threadIdx.x == 0) p.tile_base[p.n_seg] = (int32_t)carry;
+}
+
+__global__ void __launch_bounds__(256) plan_fill_kernel(Plan p) {
+  const int s = blockIdx.x;
+  const int tb = p.tile_base[s], tc = p.tile_base[s + 1] - tb;
+  for (int t = threadIdx.x; t < tc; t += blockDim.x) p.tile_seg[tb + t] = s;
+}
+
+// The tile a CTA works on.  false = this CTA is beyond the last tile (the grid is sized by max_tiles()).
+struct TileRef { int seg, tb, tc, t, count; int64_t start; };
+__device__ __forceinline__ bool locate_tile(const Plan& p, const int32_t* __restrict__ off, TileRef& r) {
+  const int tile = blockIdx.x;
+  if (tile >= p.tile_base[p.n_seg]) return false;
+  r.seg = p.tile_seg[tile];
+  r.tb = p.tile_base[r.seg];
+  r.tc = p.tile_base[r.seg + 1] - r.tb;
+  r.t = tile - r.tb;
+  r.start = (int64_t)off[r.seg] + (int64_t)r.t * kTile;
+  const int64_t left = (int64_t)off[r.seg + 1] - r.start;
+  r.count = left < kTile ? (int)left : kTile;
+  return true;
+}
+
+__global__ void __launch_bounds__(kThreads) seg_hist(const uint32_t* __restrict__ keys, const int32_t* __restrict__ off,
+                                                     Plan p, int shift, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t h[kDigits];
+  TileRef r;
+  if (!locate_tile(p, off, r)) return;
+  const int tid = threadIdx.x;
+  if (tid < kDigits) h[tid] = 0;
+  __syncthreads();
+  uint32_t k[kItems];
+#pragma unroll
+  for (int i = 0; i < kItems; i++) {
+    const int e = i * kThreads + tid;
+    k[i] = e < r.count ? keys[r.start + e] : 0u;
+  }
+#pragma unroll
+  for (int i = 0; i < kItems; i++)
+    if (i * kThreads + tid < r.count) atomicAdd(&h[(k[i] >> shift) & (kDigits - 1)], 1u);
+  __syncthreads();
+  if (tid < kDigits) hist[hist_index(r.tb, r.tc, r.t, tid)] = h[tid];
+}
+
+// ---- exclusive scan of the first kDigits * (number of tiles) table entries, in place, three small kernels
+__device__ __forceinline__ int64_t table_len(const Plan& p) { return (int64_t)kDigits * p.tile_base[p.n_seg]; }
+
+__global__ void __launch_bounds__(1024) scan_reduce(const uint32_t* __restrict__ a, Plan p, uint32_t* __restrict__ part) {
+  __shared__ uint32_t wsum[33];
+  const int64_t m = table_len(p);
+  const int64_t i0 = (int64_t)blockIdx.x * kScanChunk + (int64_t)threadIdx.x * 8;
+  if ((int64_t)blockIdx.x * kScanChunk >= m) return;
+  uint32_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) sum += (i0 + k < m) ? a[i0 + k] : 0u;
+  uint32_t total;
+  block_excl_scan_1024(sum, wsum, total);
+  if (threadIdx.x == 0) part[blockIdx.x] = total;
+}
+
+// one CTA: exclusive scan of the chunk totals (any count, 1024 x 8 at a time)
+__global__ void __launch_bounds__(1024) scan_top(uint32_t* __restrict__ part, Plan p) {
+  __shared__ uint32_t wsum[33];
+  const int64_t np = (table_len(p) + kScanChunk - 1) / kScanChunk;
+  uint32_t carry = 0;
+  for (int64_t base = 0; base < np; base += kScanChunk) {
+    uint32_t v[8], sum = 0;
+    const int64_t i0 = base + (int64_t)threadIdx.x * 8;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { v[k] = (i0 + k < np) ? part[i0 + k] : 0u; sum += v[k]; }
+    uint32_t total;
+    uint32_t run = carry + block_excl_scan_1024(sum, wsum, total);
+#pragma unroll
+    for (int k = 0; k < 8; k++) { if (i0 + k < np) part[i0 + k] = run; run += v[k]; }
+    carry += total;
+  }
+}
+
+__global__ void __launch_bounds__(1024) scan_apply(uint32_t* __restrict__ a, Plan p, const uint32_t* __restrict__ part) {
+  __shared__ uint32_t wsum[33];
+  const int64_t m = table_len(p);
+  if ((int64_t)blockIdx.x * kScanChunk >= m) return;
+  const int64_t i0 = (int64_t)blockIdx.x * kScanChunk + (int64_t)threadIdx.x * 8;
+  uint32_t v[8], sum = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) { v[k] = (i0 + k < m) ? a[i0 + k] : 0u; sum += v[k]; }
+  uint32_t total;
+  uint32_t run = part[blockIdx.x] + block_excl_scan_1024(sum, wsum, total);
+#pragma unroll
+  for (int k = 0; k < 8; k++) { if (i0 + k < m) a[i0 + k] = run; run += v[k]; }
+}
+
+inline void scan_table(uint32_t* hist, const Plan& p, int64_t n, cudaStream_t st, int* launches) {
+  const int64_t m = (int64_t)kDigits * max_tiles(n, p.n_seg);
+  const int chunks = (int)((m + kScanChunk - 1) / kScanChunk);
+  uint32_t* part = hist + m;                     // chunk totals live behind the table
+  scan_reduce<<<chunks, 1024, 0, st>>>(hist, p, part);
+  scan_top<<<1, 1024, 0, st>>>(part, p);
+  scan_apply<<<chunks, 1024, 0, st>>>(hist, p, part);
+  if (launches) *launches += 3;
+}
+
+struct StorePairs {          // the ordinary pass: write the pair to its sorted position
+  uint32_t* keys_out; uint32_t* vals_out;
+  __device__ __forceinline__ void operator()(uint32_t pos, uint32_t key, uint32_t val, int) const {
+    keys_out[pos] = key; vals_out[pos] = val;
+  }
+};
+
+// One tile: rank, sort in shared memory, write out.  kFirst: the value of element i is i itself (nothing to read).
+template <bool kFirst, class Out>
+__global__ void __launch_bounds__(kThreads) seg_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                        const int32_t* __restrict__ off, Plan p, int shift,
+                                                        const uint32_t* __restrict__ hist, Out out) {
+  __shared__ uint32_t skey[kTile], sval[kTile];
+  __shared__ uint16_t wcnt[kWarps][kDigits];     // per warp: count, then exclusive offset inside the digit's run
+  __shared__ uint32_t dstart[kDigits];           // first slot of each digit in the sorted tile
+  __shared__ uint32_t gbase[kDigits];            // global position of that slot
+  __shared__ uint32_t wtot[kDigits / 32];
+  TileRef r;
+  if (!locate_tile(p, off, r)) return;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  for (int k = tid; k < kWarps * kDigits / 2; k += kThreads) reinterpret_cast<uint32_t*>(&wcnt[0][0])[k] = 0u;
+  if (tid < kDigits) gbase[tid] = hist[hist_index(r.tb, r.tc, r.t, tid)];
+  uint32_t key[kItems];
+#pragma unroll
+  for (int i = 0; i < kItems; i++) {
+    const int e = w * kWarpSpan + i * 32 + lane;
+    key[i] = e < r.count ? keys_in[r.start + e] : 0u;
+  }
+  __syncthreads();
+  uint32_t rank2[kItems / 2];                    // two 16-bit ranks per register
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int i = 0; i < kItems; i++) {
+    const int e = w * kWarpSpan + i * 32 + lane;
+    const uint32_t d = e < r.count ? ((key[i] >> shift) & (kDigits - 1)) : (uint32_t)kDigits;
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if (lane == leader && d < kDigits) { old = wcnt[w][d]; wcnt[w][d] = (uint16_t)(old + __popc(peers)); }
+    __syncwarp();
+    old = __shfl_sync(0xffffffffu, old, leader) + __popc(peers & lt);
+    if (i & 1) rank2[i >> 1] |= old << 16; else rank2[i >> 1] = old;
+  }
+  __syncthreads();
+  uint32_t tot = 0, incl = 0;
+  if (tid < kDigits) {
+#pragma unroll
+    for (int k = 0; k < kWarps; k++) { const uint32_t c = wcnt[k][tid]; wcnt[k][tid] = (uint16_t)tot; tot += c; }
+    incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wtot[w] = incl;
+  }
+  __syncthreads();
+  if (tid < kDigits) {
+    uint32_t base = 0;
+#pragma unroll
+    for (int k = 0; k < kDigits / 32; k++) base += k < w ? wtot[k] : 0u;
+    dstart[tid] = base + incl - tot;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < kItems; i++) {
+    const int e = w * kWarpSpan + i * 32 + lane;
+    if (e < r.count) {
+      const uint32_t d = (key[i] >> shift) & (kDigits - 1);
+      const uint32_t rk = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xFFFFu);
+      const uint32_t slot = dstart[d] + wcnt[w][d] + rk;
+      skey[slot] = key[i];
+      sval[slot] = kFirst ? (uint32_t)(r.start + e) : vals_in[r.start + e];
+    }
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int i = 0; i < kItems; i++) {
+    const int slot = i * kThreads + tid;
+    if (slot < r.count) {
+      const uint32_t k = skey[slot];
+      const uint32_t d = (k >> shift) & (kDigits - 1);
+      out(gbase[d] + ((uint32_t)slot - dstart[d]), k, sval[slot], r.seg);
+    }
+  }
+}
+
+}  // namespace ssort
