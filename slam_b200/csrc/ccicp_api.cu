@@ -36,7 +36,7 @@ struct ccicp_ctx {
   void* timed_stream = nullptr;
   DevBuf counter, scratch, all_results, workspace;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
-  DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap, c_tile_base, c_tile_seg;            // classification scratch
+  DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap, c_tile_base, c_tile_seg, c_group_base;            // classification scratch
   DevBuf l_src, l_soff, l_tgt, l_toff, l_dist, l_idx, l_info, l_num, l_status;   // Lu-Milios edge information
   DevBuf c_xyz, c_off, c_out_xyz, c_out_ga, c_out_src, c_out_cnt;             // classification, host-buffer path
   ccicp_launch_info info{};
@@ -267,7 +267,7 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
-                    &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_tile_base, &ctx->c_tile_seg, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
+                    &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_tile_base, &ctx->c_tile_seg, &ctx->c_group_base, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
                     &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
                     &ctx->l_dist, &ctx->l_idx, &ctx->l_info, &ctx->l_num, &ctx->l_status};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -481,11 +481,12 @@ int ccicp_classify_points_device(ccicp_ctx* ctx, int32_t n_clouds, const float* 
   if ((rc = reserve(ctx, ctx->c_vals_tmp, nb))) return rc;
   if ((rc = reserve(ctx, ctx->c_hist, classify::hist_words(n_points, n_clouds) * 4))) return rc;
   if ((rc = reserve(ctx, ctx->c_tile_base, ((size_t)n_clouds + 1) * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->c_group_base, ((size_t)n_clouds + 1) * 4))) return rc;
   if ((rc = reserve(ctx, ctx->c_tile_seg, ((size_t)ssort::max_tiles(n_points, n_clouds) + 1) * 4))) return rc;
   if ((rc = reserve(ctx, ctx->c_bitmap, (size_t)n_clouds * classify::kWordsPerCloud * 4))) return rc;
   classify::Scratch sc{(uint32_t*)ctx->c_keys.p, (uint32_t*)ctx->c_vals.p, (uint32_t*)ctx->c_keys_tmp.p,
                        (uint32_t*)ctx->c_vals_tmp.p, (uint32_t*)ctx->c_hist.p, (uint32_t*)ctx->c_bitmap.p,
-                       (int32_t*)ctx->c_tile_base.p, (int32_t*)ctx->c_tile_seg.p};
+                       (int32_t*)ctx->c_tile_base.p, (int32_t*)ctx->c_tile_seg.p, (int32_t*)ctx->c_group_base.p};
   CK(cudaEventRecord(ctx->ev[2], st));
   ctx->info.n_launches = classify::run(d_xyz, d_cloud_off, n_clouds, n_points, sc, d_out_xyz, d_out_ground_adj,
                                        d_out_src_index, d_out_count, st);

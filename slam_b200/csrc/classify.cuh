@@ -1,8 +1,9 @@
 // classify.cuh -- GA / NGA classification of segmented obstacle points on the GPU
 // (CCICP::classifyPoints, ccicp2d/src/icpTools.cpp:36-103; constants icpTools.h:24-26): SURVEY.md 8(f) rank 2.
 //
-//   classify_key_kernel   one CTA per tile of 4096 points of one cloud: bin index with the reference's double
-//                         arithmetic, occupancy bit (per-cloud bitmap, 1200 x 1200 bits = 180 KB), sort key = bin;
+//   classify_key_kernel   one CTA per <= 32 tiles of 4096 points of one cloud: bin index with the reference's double
+//                         arithmetic, occupancy bit (per-cloud bitmap, 1200 x 1200 bits = 180 KB, gathered in shared
+//                         memory first), sort key = bin;
 //                         points the reference drops (outside the grid, NaN, outermost ring of bins) get the largest
 //                         key so they end up behind the kept points of their cloud.  Also produces the digit
 //                         histogram of the first radix pass and the per-cloud count of kept points.
@@ -28,82 +29,115 @@ static_assert(3 * ssort::kBits == 21, "three radix passes cover the 21-bit bin i
 constexpr int kWordsPerCloud = (kBins * kBins + 31) / 32;
 constexpr int kMaxClouds = 2048;            // bitmap memory: 180 KB per cloud
 
-__global__ void __launch_bounds__(ssort::kThreads) classify_key_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ off,
+// One CTA per group of up to 32 tiles of one cloud.  The cloud's occupancy bitmap is accumulated in SHARED memory
+// (180 KB) and only its non-zero words go to the global bitmap: one global atomic per point -- 17.9 M scattered REDs --
+// cost 100 us of a 155 us kernel, the points of a cloud touch ~7x fewer distinct words.
+constexpr int kKeyThreads = 1024;
+constexpr int kKeyItems = ssort::kTile / kKeyThreads;          // points per thread per tile
+constexpr size_t kKeySmemBytes = (size_t)kWordsPerCloud * 4 + 4 * ssort::kDigits * 4;
+
+__global__ void __launch_bounds__(kKeyThreads, 1) classify_key_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ off,
                                                                       ssort::Plan plan, uint32_t* __restrict__ keys,
                                                                       uint32_t* __restrict__ bitmap, uint32_t* __restrict__ hist,
                                                                       int32_t* __restrict__ out_count) {
-  __shared__ uint32_t h[ssort::kDigits];
+  extern __shared__ __align__(16) uint32_t key_smem[];
+  uint32_t* sbm = key_smem;                                    // [kWordsPerCloud]
+  uint32_t* h = key_smem + kWordsPerCloud;                     // [4][kDigits]: two tiles in flight, double buffered
   __shared__ int kept_s;
-  ssort::TileRef r;
-  if (!ssort::locate_tile(plan, off, r)) return;
+  const int group = blockIdx.x;
+  if (group >= plan.group_base[plan.n_seg]) return;
+  const int seg = ssort::seg_of(plan.group_base, plan.n_seg, group);
+  const int gb = plan.group_base[seg], ng = plan.group_base[seg + 1] - gb;
+  const int tb = plan.tile_base[seg], tc = plan.tile_base[seg + 1] - tb;
+  const int t0 = (int)((int64_t)(group - gb) * tc / ng), t1 = (int)((int64_t)(group - gb + 1) * tc / ng);
+  const int64_t seg_start = off[seg], seg_end = off[seg + 1];
   const int tid = threadIdx.x;
-  if (tid < ssort::kDigits) h[tid] = 0;
+  for (int k = tid; k < kWordsPerCloud / 4; k += kKeyThreads) reinterpret_cast<uint4*>(sbm)[k] = make_uint4(0u, 0u, 0u, 0u);
+  if (tid < 4 * ssort::kDigits) h[tid] = 0;
   if (tid == 0) kept_s = 0;
   __syncthreads();
-  float x[ssort::kItems], y[ssort::kItems];
-#pragma unroll
-  for (int k = 0; k < ssort::kItems; k++) {
-    const int e = k * ssort::kThreads + tid;
-    const size_t i = (size_t)(r.start + e);
-    x[k] = e < r.count ? xyz[3 * i] : 0.0f;
-    y[k] = e < r.count ? xyz[3 * i + 1] : 0.0f;
-  }
-  uint32_t* bm = bitmap + (size_t)r.seg * kWordsPerCloud;
   int kept = 0;
+  for (int t = t0, pair = 0; t < t1; t += 2, pair++) {
+    uint32_t* h2 = h + (pair & 1) * 2 * ssort::kDigits;         // histograms of tiles t and t + 1
+    float x[2 * kKeyItems], y[2 * kKeyItems];
 #pragma unroll
-  for (int k = 0; k < ssort::kItems; k++) {
-    const int e = k * ssort::kThreads + tid;
-    if (e >= r.count) continue;
-    // icpTools.cpp:44-52: offset = NUMBINSGA*RESOLUTION/2 (double); floor((float + double) / double)
-    const double offset = (double)kBins * kRes / 2.0;
-    const double fx = floor(((double)x[k] + offset) / kRes), fy = floor(((double)y[k] + offset) / kRes);
-    uint32_t bin = kDropped;
-    if (fx >= 0.0 && fx < (double)kBins && fy >= 0.0 && fy < (double)kBins) {       // false for NaN
-      const int bx = (int)fx, by = (int)fy;
-      const int hh = bx * kBins + by;                                               // :55
-      atomicOr(&bm[hh >> 5], 1u << (hh & 31));
-      if (bx != 0 && bx != kBins - 1 && by != 0 && by != kBins - 1) { bin = (uint32_t)hh; kept++; }   // :72-77 border bins are not emitted
+    for (int k = 0; k < 2 * kKeyItems; k++) {
+      const int64_t i = seg_start + (int64_t)(t + k / kKeyItems) * ssort::kTile + (k % kKeyItems) * kKeyThreads + tid;
+      const bool in = i < seg_end && t + k / kKeyItems < t1;
+      x[k] = in ? xyz[3 * (size_t)i] : 0.0f;
+      y[k] = in ? xyz[3 * (size_t)i + 1] : 0.0f;
     }
-    keys[r.start + e] = bin;
-    atomicAdd(&h[bin & (ssort::kDigits - 1)], 1u);
+#pragma unroll
+    for (int k = 0; k < 2 * kKeyItems; k++) {
+      const int64_t i = seg_start + (int64_t)(t + k / kKeyItems) * ssort::kTile + (k % kKeyItems) * kKeyThreads + tid;
+      if (!(i < seg_end && t + k / kKeyItems < t1)) continue;
+      // icpTools.cpp:44-52: offset = NUMBINSGA*RESOLUTION/2 (double); floor((float + double) / double)
+      const double offset = (double)kBins * kRes / 2.0;
+      const double fx = floor(((double)x[k] + offset) / kRes), fy = floor(((double)y[k] + offset) / kRes);
+      uint32_t bin = kDropped;
+      if (fx >= 0.0 && fx < (double)kBins && fy >= 0.0 && fy < (double)kBins) {     // false for NaN
+        const int bx = (int)fx, by = (int)fy;
+        const int hh = bx * kBins + by;                                             // :55
+        atomicOr(&sbm[hh >> 5], 1u << (hh & 31));
+        if (bx != 0 && bx != kBins - 1 && by != 0 && by != kBins - 1) { bin = (uint32_t)hh; kept++; }   // :72-77 border bins are not emitted
+      }
+      keys[i] = bin;
+      atomicAdd(&h2[(k / kKeyItems) * ssort::kDigits + (bin & (ssort::kDigits - 1))], 1u);
+    }
+    __syncthreads();
+    if (tid < 2 * ssort::kDigits) {              // write the pair's histograms out, clear them for the pair after next
+      const int tt = t + tid / ssort::kDigits;
+      if (tt < t1) hist[ssort::hist_index(tb, tc, tt, tid % ssort::kDigits)] = h2[tid];
+      h2[tid] = 0;
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) kept += __shfl_xor_sync(0xffffffffu, kept, o);
   if ((tid & 31) == 0 && kept) atomicAdd(&kept_s, kept);
   __syncthreads();
-  if (tid < ssort::kDigits) hist[ssort::hist_index(r.tb, r.tc, r.t, tid)] = h[tid];
-  if (tid == 0 && kept_s) atomicAdd(&out_count[r.seg], kept_s);
+  uint32_t* bm = bitmap + (size_t)seg * kWordsPerCloud;
+  for (int k = tid; k < kWordsPerCloud; k += kKeyThreads) {
+    const uint32_t v = sbm[k];
+    if (v) { if (ng == 1) bm[k] = v; else atomicOr(&bm[k], v); }
+  }
+  if (tid == 0 && kept_s) atomicAdd(&out_count[seg], kept_s);
 }
 
 // Consumer of the last radix pass: element `src` (global input index) of cloud `c` lands at sorted position `pos`.
 struct EmitPoint {
   const float* __restrict__ xyz; const int32_t* __restrict__ off; const uint32_t* __restrict__ bitmap;
   float* __restrict__ out_xyz; uint8_t* __restrict__ out_ga; int32_t* __restrict__ out_src;
-  __device__ __forceinline__ void operator()(uint32_t pos, uint32_t bin, uint32_t src, int c) const {
-    if (bin == kDropped) return;
+  struct Item { float x, y, z; uint32_t rows[3]; };
+  // rows[q]: bits (by-1, by, by+1) of bitmap row bx-1+q in its low three bits
+  __device__ __forceinline__ Item fetch(uint32_t, uint32_t bin, uint32_t src, int c) const {
+    Item it{0.0f, 0.0f, 0.0f, {0u, 0u, 0u}};
+    if (bin == kDropped) return it;
     const int bx = (int)(bin / kBins), by = (int)(bin % kBins);
     const uint32_t* bm = bitmap + (size_t)c * kWordsPerCloud;
-    int empty = 0;                                                                  // :79-90
 #pragma unroll
-    for (int dq = -1; dq <= 1; dq++) {
-#pragma unroll
-      for (int dr = -1; dr <= 1; dr++) {
-        if (dq == 0 && dr == 0) continue;
-        const int hh = (bx + dq) * kBins + (by + dr);
-        empty += ((bm[hh >> 5] >> (hh & 31)) & 1u) ? 0 : 1;
-      }
+    for (int q = 0; q < 3; q++) {
+      const int h0 = (bx - 1 + q) * kBins + (by - 1);            // >= 0: border bins are never emitted
+      const uint32_t lo = bm[h0 >> 5], hi = bm[(h0 + 2) >> 5];   // same word unless the window straddles
+      it.rows[q] = __funnelshift_r(lo, ((h0 + 2) >> 5) != (h0 >> 5) ? hi : 0u, h0 & 31) & 7u;
     }
-    const size_t s3 = 3 * (size_t)src, p3 = 3 * (size_t)pos;
-    const float px = xyz[s3], py = xyz[s3 + 1], pz = xyz[s3 + 2];
-    out_xyz[p3] = px; out_xyz[p3 + 1] = py; out_xyz[p3 + 2] = pz;
-    out_ga[pos] = empty >= kAdjThresh ? 1 : 0;                                      // :98
+    const size_t s3 = 3 * (size_t)src;
+    it.x = xyz[s3]; it.y = xyz[s3 + 1]; it.z = xyz[s3 + 2];
+    return it;
+  }
+  __device__ __forceinline__ void commit(uint32_t pos, uint32_t bin, uint32_t src, int c, const Item& it) const {
+    if (bin == kDropped) return;
+    // icpTools.cpp:79-90: empty bins among the 8 neighbours
+    const int occupied = __popc(it.rows[0]) + __popc(it.rows[1] & 5u) + __popc(it.rows[2]);
+    const size_t p3 = 3 * (size_t)pos;
+    out_xyz[p3] = it.x; out_xyz[p3 + 1] = it.y; out_xyz[p3 + 2] = it.z;
+    out_ga[pos] = (8 - occupied) >= kAdjThresh ? 1 : 0;          // :98
     if (out_src) out_src[pos] = (int32_t)((int64_t)src - off[c]);
   }
 };
 
 struct Scratch {          // device pointers, sized by the caller
   uint32_t *keys, *vals, *keys_tmp, *vals_tmp, *hist, *bitmap;
-  int32_t *tile_base, *tile_seg;              // [n_clouds + 1], [ssort::max_tiles(n, n_clouds)]
+  int32_t *tile_base, *tile_seg, *group_base; // [n_clouds + 1], [ssort::max_tiles(n, n_clouds)], [n_clouds + 1]
 };
 
 inline size_t hist_words(int64_t n, int n_clouds) { return ssort::hist_words(n, n_clouds); }
@@ -115,12 +149,13 @@ inline int run(const float* d_xyz, const int32_t* d_off, int n_clouds, int64_t n
   cudaMemsetAsync(s.bitmap, 0, (size_t)n_clouds * kWordsPerCloud * 4, st);
   cudaMemsetAsync(d_out_count, 0, (size_t)n_clouds * 4, st);
   if (n <= 0) return 0;
-  const ssort::Plan plan{s.tile_base, s.tile_seg, n_clouds};
+  const ssort::Plan plan{s.tile_base, s.tile_seg, s.group_base, n_clouds};
   const int tiles = ssort::max_tiles(n, n_clouds);
   ssort::plan_kernel<<<1, 1024, 0, st>>>(d_off, plan);
-  ssort::plan_fill_kernel<<<n_clouds, 256, 0, st>>>(plan);
-  classify_key_kernel<<<tiles, ssort::kThreads, 0, st>>>(d_xyz, d_off, plan, s.keys, s.bitmap, s.hist, d_out_count);
-  launches += 3;
+  cudaFuncSetAttribute(classify_key_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKeySmemBytes);   // per device
+  classify_key_kernel<<<ssort::max_groups(n, n_clouds), kKeyThreads, kKeySmemBytes, st>>>(d_xyz, d_off, plan, s.keys, s.bitmap, s.hist,
+                                                                                         d_out_count);
+  launches += 2;
   // pass 0 (bits 0-6): values implicit; pass 1 (7-13); pass 2 (14-20) emits
   ssort::scan_table(s.hist, plan, n, st, &launches);
   ssort::seg_scatter<true, ssort::StorePairs><<<tiles, ssort::kThreads, 0, st>>>(s.keys, nullptr, d_off, plan, 0, s.hist,

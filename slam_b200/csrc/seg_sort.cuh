@@ -8,7 +8,7 @@
 // 7 bits per pass (three passes for the 21-bit bin index).  Per pass:
 //   seg_hist     per-tile digit histogram                       (pass 0: produced by the caller's key kernel)
 //   scan_*       exclusive scan of the table (chunk totals, scan of totals, per-chunk scan)
-//   seg_scatter  ranks the tile's elements (match_any inside a warp + per-warp digit counters, warp w owns the
+//   seg_scatter  ranks the tile's elements (ballot peer masks inside a warp + per-warp digit counters, warp w owns the
 //                w-th contiguous 512 elements so the counters need no block barrier between rounds), sorts the tile
 //                in shared memory and writes runs of equal digits to consecutive addresses.  The last pass hands
 //                (position, key, value) to a functor instead of storing the pair: the consumer is fused in.
@@ -27,14 +27,18 @@ constexpr int kWarpSpan = kTile / kWarps;       // 512 consecutive elements per 
 constexpr int kBits = 7;
 constexpr int kDigits = 1 << kBits;
 
-struct Plan {                // device arrays, filled by plan_kernel / plan_fill_kernel
+struct Plan {                // device arrays, filled by plan_kernel
   int32_t* tile_base;        // [n_seg + 1] first tile of each segment; tile_base[n_seg] = number of tiles
   int32_t* tile_seg;         // [max_tiles] segment of each tile
+  int32_t* group_base;       // [n_seg + 1] or NULL: first tile GROUP of each segment (a segment's tiles split evenly into
+                             // ceil(tiles / kGroupTiles) groups, for kernels that want one CTA per many tiles)
   int32_t n_seg;
 };
+constexpr int kGroupTiles = 32;
 
 // sum over segments of ceil(n_s / kTile) <= n / kTile + n_seg
 __host__ __device__ inline int max_tiles(int64_t n, int n_seg) { return (int)(n / kTile) + n_seg; }
+__host__ __device__ inline int max_groups(int64_t n, int n_seg) { return max_tiles(n, n_seg) / kGroupTiles + n_seg; }
 constexpr int kScanChunk = 1024 * 8;            // table entries per scan CTA: 1024 threads x 8
 __host__ __device__ inline size_t hist_words(int64_t n, int n_seg) {
   const size_t m = (size_t)kDigits * max_tiles(n, n_seg);
@@ -64,10 +68,19 @@ __device__ __forceinline__ uint32_t block_excl_scan_1024(uint32_t sum, uint32_t*
   return wsum[w] + incl - sum;
 }
 
-// ---- tiling plan: one CTA scans the per-segment tile counts, a second kernel labels the tiles
+// ---- tiling plan (one CTA): scan of the per-segment tile (and group) counts, then the tile -> segment labels
+__device__ __forceinline__ int seg_of(const int32_t* base, int n_seg, int i) {
+  int lo = 0, hi = n_seg;                    // largest s with base[s] <= i (empty segments share a base: take the last)
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (base[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
 __global__ void __launch_bounds__(1024) plan_kernel(const int32_t* __restrict__ off, Plan p) {
   __shared__ uint32_t wsum[33];
-  uint32_t carry = 0;
+  uint32_t carry = 0, gcarry = 0;
   for (int base = 0; base < p.n_seg; base += 1024) {
     const int s = base + threadIdx.x;
     const uint32_t t = s < p.n_seg ? (uint32_t)((off[s + 1] - off[s] + kTile - 1) / kTile) : 0u;
@@ -75,14 +88,19 @@ __global__ void __launch_bounds__(1024) plan_kernel(const int32_t* __restrict__ 
     const uint32_t ex = block_excl_scan_1024(t, wsum, total);
     if (s < p.n_seg) p.tile_base[s] = (int32_t)(carry + ex);
     carry += total;
+    if (p.group_base) {
+      const uint32_t g = (t + kGroupTiles - 1) / kGroupTiles;
+      const uint32_t gex = block_excl_scan_1024(g, wsum, total);
+      if (s < p.n_seg) p.group_base[s] = (int32_t)(gcarry + gex);
+      gcarry += total;
+    }
   }
-  if (threadIdx.x == 0) p.tile_base[p.n_seg] = (int32_t)carry;
-}
-
-__global__ void __launch_bounds__(256) plan_fill_kernel(Plan p) {
-  const int s = blockIdx.x;
-  const int tb = p.tile_base[s], tc = p.tile_base[s + 1] - tb;
-  for (int t = threadIdx.x; t < tc; t += blockDim.x) p.tile_seg[tb + t] = s;
+  if (threadIdx.x == 0) {
+    p.tile_base[p.n_seg] = (int32_t)carry;
+    if (p.group_base) p.group_base[p.n_seg] = (int32_t)gcarry;
+  }
+  __syncthreads();                             // this CTA's global writes above are visible to all its threads
+  for (int t = threadIdx.x; t < (int)carry; t += 1024) p.tile_seg[t] = seg_of(p.tile_base, p.n_seg, t);
 }
 
 // The tile a CTA works on.  false = this CTA is beyond the last tile (the grid is sized by max_tiles()).
@@ -179,16 +197,21 @@ inline void scan_table(uint32_t* hist, const Plan& p, int64_t n, cudaStream_t st
   if (launches) *launches += 3;
 }
 
+// Consumers of a scatter pass are split in fetch (loads only) and commit (stores only) so that the loads of a batch of
+// elements are all in flight before the first store: nothing here may alias, but the compiler cannot know that.
 struct StorePairs {          // the ordinary pass: write the pair to its sorted position
   uint32_t* keys_out; uint32_t* vals_out;
-  __device__ __forceinline__ void operator()(uint32_t pos, uint32_t key, uint32_t val, int) const {
+  struct Item {};
+  __device__ __forceinline__ Item fetch(uint32_t, uint32_t, uint32_t, int) const { return Item{}; }
+  __device__ __forceinline__ void commit(uint32_t pos, uint32_t key, uint32_t val, int, const Item&) const {
     keys_out[pos] = key; vals_out[pos] = val;
   }
 };
+constexpr int kOutBatch = 4;
 
 // One tile: rank, sort in shared memory, write out.  kFirst: the value of element i is i itself (nothing to read).
 template <bool kFirst, class Out>
-__global__ void __launch_bounds__(kThreads) seg_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+__global__ void __launch_bounds__(kThreads, 4) seg_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                         const int32_t* __restrict__ off, Plan p, int shift,
                                                         const uint32_t* __restrict__ hist, Out out) {
   __shared__ uint32_t skey[kTile], sval[kTile];
@@ -208,19 +231,39 @@ __global__ void __launch_bounds__(kThreads) seg_scatter(const uint32_t* __restri
     key[i] = e < r.count ? keys_in[r.start + e] : 0u;
   }
   __syncthreads();
+  // Rank inside the warp's span.  The peer mask (lanes of this round with the same digit) is built from one ballot per
+  // digit bit -- MATCH.ANY has a latency of several hundred cycles here and the ballots of eight rounds pipeline.
   uint32_t rank2[kItems / 2];                    // two 16-bit ranks per register
   const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-  for (int i = 0; i < kItems; i++) {
-    const int e = w * kWarpSpan + i * 32 + lane;
-    const uint32_t d = e < r.count ? ((key[i] >> shift) & (kDigits - 1)) : (uint32_t)kDigits;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
-    const int leader = __ffs(peers) - 1;
-    uint32_t old = 0;
-    if (lane == leader && d < kDigits) { old = wcnt[w][d]; wcnt[w][d] = (uint16_t)(old + __popc(peers)); }
-    __syncwarp();
-    old = __shfl_sync(0xffffffffu, old, leader) + __popc(peers & lt);
-    if (i & 1) rank2[i >> 1] |= old << 16; else rank2[i >> 1] = old;
+  for (int half = 0; half < 2; half++) {
+    uint32_t pm[kItems / 2];
+#pragma unroll
+    for (int j = 0; j < kItems / 2; j++) {
+      const int i = half * (kItems / 2) + j;
+      const bool valid = w * kWarpSpan + i * 32 + lane < r.count;
+      const uint32_t d = (key[i] >> shift) & (kDigits - 1);
+      uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+      for (int b = 0; b < kBits; b++) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+      }
+      pm[j] = peers;
+    }
+#pragma unroll
+    for (int j = 0; j < kItems / 2; j++) {
+      const int i = half * (kItems / 2) + j;
+      const bool valid = w * kWarpSpan + i * 32 + lane < r.count;
+      const uint32_t d = (key[i] >> shift) & (kDigits - 1);
+      const uint32_t before = __popc(pm[j] & lt);
+      const uint32_t old = valid ? (uint32_t)wcnt[w][d] : 0u;
+      __syncwarp();
+      if (valid && before == 0) wcnt[w][d] = (uint16_t)(old + __popc(pm[j]));   // lowest peer lane updates the counter
+      __syncwarp();
+      if (i & 1) rank2[i >> 1] |= (old + before) << 16; else rank2[i >> 1] = old + before;
+    }
   }
   __syncthreads();
   uint32_t tot = 0, incl = 0;
@@ -252,14 +295,22 @@ __global__ void __launch_bounds__(kThreads) seg_scatter(const uint32_t* __restri
     }
   }
   __syncthreads();
-#pragma unroll 4
-  for (int i = 0; i < kItems; i++) {
-    const int slot = i * kThreads + tid;
-    if (slot < r.count) {
-      const uint32_t k = skey[slot];
-      const uint32_t d = (k >> shift) & (kDigits - 1);
-      out(gbase[d] + ((uint32_t)slot - dstart[d]), k, sval[slot], r.seg);
+  for (int i0 = 0; i0 < kItems; i0 += kOutBatch) {
+    uint32_t k[kOutBatch], v[kOutBatch], pos[kOutBatch];
+    typename Out::Item item[kOutBatch];
+#pragma unroll
+    for (int j = 0; j < kOutBatch; j++) {
+      const int slot = (i0 + j) * kThreads + tid;
+      if (slot < r.count) {
+        k[j] = skey[slot]; v[j] = sval[slot];
+        const uint32_t d = (k[j] >> shift) & (kDigits - 1);
+        pos[j] = gbase[d] + ((uint32_t)slot - dstart[d]);
+        item[j] = out.fetch(pos[j], k[j], v[j], r.seg);
+      }
     }
+#pragma unroll
+    for (int j = 0; j < kOutBatch; j++)
+      if ((i0 + j) * kThreads + tid < r.count) out.commit(pos[j], k[j], v[j], r.seg, item[j]);
   }
 }
 
