@@ -39,3 +39,39 @@ def test_edges_nan_and_duplicates(ctx):
 
 def test_many_small_clouds(ctx):
     _check(ctx, [synthetic_cloud(100 + k, 300) for k in range(300)])
+
+
+def _device_call(ctx, clouds, misalign_floats=0):
+    import torch
+    dev = torch.device("cuda", 0)
+    off = np.cumsum([0] + [len(c) for c in clouds]).astype(np.int32)
+    xyz = np.concatenate(clouds, 0)
+    n = len(xyz)
+    buf = torch.zeros(3 * n + 4, dtype=torch.float32, device=dev)
+    d_xyz = buf[misalign_floats:misalign_floats + 3 * n]
+    d_xyz.copy_(torch.from_numpy(xyz.reshape(-1)).to(dev))
+    d_off = torch.from_numpy(off).to(dev)
+    o_xyz = torch.empty(3 * n, dtype=torch.float32, device=dev); o_ga = torch.empty(n, dtype=torch.uint8, device=dev)
+    o_src = torch.empty(n, dtype=torch.int32, device=dev); o_cnt = torch.empty(len(clouds), dtype=torch.int32, device=dev)
+    ctx.classify_points_device(len(clouds), d_xyz.data_ptr(), d_off.data_ptr(), n, o_xyz.data_ptr(), o_ga.data_ptr(),
+                               o_src.data_ptr(), o_cnt.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    o_xyz, o_ga, o_src, o_cnt = (t.cpu().numpy() for t in (o_xyz.view(n, 3), o_ga, o_src, o_cnt))
+    for k, c in enumerate(clouds):
+        wx, wg, ws = cp.classify(c)
+        assert o_cnt[k] == len(wx)
+        sl = slice(off[k], off[k] + len(wx))
+        assert np.array_equal(o_src[sl], ws) and np.array_equal(o_ga[sl], wg)
+        assert np.array_equal(o_xyz[sl].view(np.uint32), wx.view(np.uint32))
+
+
+def test_device_api_gather_paths(ctx):
+    """Device-pointer entry point, with an 8-byte aligned and a merely 4-byte aligned xyz pointer."""
+    clouds = [synthetic_cloud(7, 9001), synthetic_cloud(8, 4096), synthetic_cloud(9, 777)]
+    _device_call(ctx, clouds, 0)
+    _device_call(ctx, clouds, 1)
+
+
+def test_one_large_cloud_spans_several_tile_groups(ctx):
+    """> 32 tiles: the key kernel splits the cloud over several CTAs that merge their bitmaps with atomics."""
+    _device_call(ctx, [synthetic_cloud(11, 300000), synthetic_cloud(12, 50)], 0)
