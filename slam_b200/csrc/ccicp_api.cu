@@ -30,6 +30,7 @@ struct ccicp_ctx {
   cudaEvent_t chunk_ev[16] = {};
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
   bool timed = false, timed_copies = false;
+  bool chunk_ramp = true;     // CCICP_CHUNK_RAMP=0: equal chunks
   int chunk_pairs = 384;      // CCICP_CHUNK_PAIRS: pairs per H2D/compute chunk of the host-buffer call
   int stage_kb = 200;         // CCICP_STAGE_KB
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the L2 variant
@@ -242,6 +243,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   ctx->device = device;
   { const char* e = getenv("CCICP_FORCE_L2"); ctx->force_l2 = e && e[0] == '1'; }
   { const char* e = getenv("CCICP_CHUNK_PAIRS"); if (e && atoi(e) >= 16) ctx->chunk_pairs = atoi(e); }
+  { const char* e = getenv("CCICP_CHUNK_RAMP"); if (e) ctx->chunk_ramp = atoi(e) != 0; }
   { const char* e = getenv("CCICP_STAGE_KB"); if (e && atoi(e) >= 1 && atoi(e) <= 216) ctx->stage_kb = atoi(e); }
   cudaDeviceProp prop;
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
@@ -361,17 +363,28 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   // chunks run on two compute streams so the tail of one kernel overlaps the head of the next.  The offsets
   // are absolute, so every chunk's kernel indexes the same device arrays with a different pair_base.
   int n_chunks = 1;
-  if (n_seeds == 1 && !corr_idx) {
-    n_chunks = n_pairs / ctx->chunk_pairs;       // up to 4 chunk kernels are in flight (4 streams, 4 scratch slots)
-    if (n_chunks > 16) n_chunks = 16;
-    if (n_chunks < 1) n_chunks = 1;
+  int32_t bound[17] = {0};
+  bound[1] = n_pairs;
+  if (n_seeds == 1 && !corr_idx && n_pairs >= 2 * ctx->chunk_pairs) {
+    // up to 4 chunk kernels are in flight (4 streams, 4 scratch slots).  The first chunks are short so that the first
+    // kernel starts after a short copy; the copies outpace the kernels, so the GPU is full a few chunks later.
+    const int cp = ctx->chunk_pairs;
+    n_chunks = 0;
+    int32_t pos = 0;
+    if (n_pairs >= 4 * cp && ctx->chunk_ramp)
+      for (int sz : {cp / 6, cp / 3, 2 * cp / 3}) { if (sz >= 16) { pos += sz; bound[++n_chunks] = pos; } }
+    int rest = (n_pairs - pos) / cp;
+    if (rest > 16 - n_chunks) rest = 16 - n_chunks;
+    if (rest < 1) rest = 1;
+    for (int c = 1; c <= rest; c++) bound[n_chunks + c] = pos + (int32_t)((int64_t)(n_pairs - pos) * c / rest);
+    n_chunks += rest;
   }
   cudaStream_t cs = ctx->copy_stream;
   CK(cudaEventRecord(ctx->ev[0], cs));
   CK(cudaMemcpyAsync(ctx->d_moff.p, model_off, off_bytes, cudaMemcpyHostToDevice, cs));
   CK(cudaMemcpyAsync(ctx->d_soff.p, scene_off, off_bytes, cudaMemcpyHostToDevice, cs));
   for (int c = 0; c < n_chunks; c++) {
-    const int32_t p0 = (int32_t)((int64_t)n_pairs * c / n_chunks), p1 = (int32_t)((int64_t)n_pairs * (c + 1) / n_chunks);
+    const int32_t p0 = bound[c], p1 = bound[c + 1];
     const int64_t m0 = model_off[2 * (size_t)p0], m1 = model_off[2 * (size_t)p1];
     const int64_t s0 = scene_off[2 * (size_t)p0], s1 = scene_off[2 * (size_t)p1];
     if (m1 > m0) CK(cudaMemcpyAsync((char*)ctx->d_model.p + m0 * 16, model_xy + 2 * m0, (size_t)(m1 - m0) * 16, cudaMemcpyHostToDevice, cs));
