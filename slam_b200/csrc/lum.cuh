@@ -77,8 +77,21 @@ __device__ inline bool solve6(const double* MM, const double* MZ, double* D) {
   return true;
 }
 
+// un-fused float ((dx*dx + dy*dy) + dz*dz), the order the sums of squares are taken in throughout this file
+__device__ __forceinline__ float dist3(const float3& p, float x, float y, float z) {
+  const float dx = __fsub_rn(p.x, x), dy = __fsub_rn(p.y, y), dz = __fsub_rn(p.z, z);
+  return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+// lowest index in the group of four starting at g whose distance equals the group minimum
+__device__ __forceinline__ int first_equal(const float3& p, const float* tx, const float* ty, const float* tz, int g, float best) {
+#pragma unroll
+  for (int k = 0; k < 3; k++)
+    if (dist3(p, tx[g + k], ty[g + k], tz[g + k]) == best) return g + k;
+  return g + 3;
+}
+
 __global__ void __launch_bounds__(kThreads) lum_edge_kernel(const Args a) {
-  __shared__ float tx[kTile], ty[kTile], tz[kTile];
+  __shared__ __align__(16) float tx[kTile], ty[kTile], tz[kTile];
   __shared__ double red[kWarps * kSums];
   __shared__ double Dsh[6];
   __shared__ int flag_sh;
@@ -97,18 +110,32 @@ __global__ void __launch_bounds__(kThreads) lum_edge_kernel(const Args a) {
         ty[j] = a.target_xyz[3 * (size_t)(t0 + tb + j) + 1];
         tz[j] = a.target_xyz[3 * (size_t)(t0 + tb + j) + 2];
       }
+      const int m4 = (m + 3) & ~3;               // pad the last group of four: distance +inf, never selected
+      if (tid < m4 - m) { tx[m + tid] = CUDART_INF_F; ty[m + tid] = CUDART_INF_F; tz[m + tid] = CUDART_INF_F; }
       __syncthreads();
-      for (int i = tid; i < ns; i += kThreads) {
-        const float sx = src[i].x, sy = src[i].y, sz = src[i].z;
-        float best = a.nn_dist[s0 + i];
-        int bi = a.nn_idx[s0 + i];
-#pragma unroll 4
-        for (int j = 0; j < m; j++) {
-          const float dx = __fsub_rn(sx, tx[j]), dy = __fsub_rn(sy, ty[j]), dz = __fsub_rn(sz, tz[j]);
-          const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-          if (d < best) { best = d; bi = tb + j; }
+      // Two source points per thread share every target load; per group of four targets only the group minimum is
+      // compared with the incumbent (3 FMNMX + 1 compare instead of 4 compare + 8 select), the index inside the winning
+      // group is resolved once per tile by recomputing its four distances (bit-identical: same un-fused operations).
+      for (int i = tid; i < ns; i += 2 * kThreads) {
+        const int i1 = i + kThreads;
+        const bool has1 = i1 < ns;
+        const float3 p0 = src[i], p1 = has1 ? src[i1] : make_float3(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F);
+        float best0 = a.nn_dist[s0 + i], best1 = has1 ? a.nn_dist[s0 + i1] : 0.0f;
+        int g0 = -1, g1 = -1;
+#pragma unroll 2
+        for (int j = 0; j < m4; j += 4) {
+          const float4 X = *reinterpret_cast<const float4*>(&tx[j]), Y = *reinterpret_cast<const float4*>(&ty[j]),
+                       Z = *reinterpret_cast<const float4*>(&tz[j]);
+          const float a0 = dist3(p0, X.x, Y.x, Z.x), a1 = dist3(p0, X.y, Y.y, Z.y), a2 = dist3(p0, X.z, Y.z, Z.z),
+                      a3 = dist3(p0, X.w, Y.w, Z.w);
+          const float b0 = dist3(p1, X.x, Y.x, Z.x), b1 = dist3(p1, X.y, Y.y, Z.y), b2 = dist3(p1, X.z, Y.z, Z.z),
+                      b3 = dist3(p1, X.w, Y.w, Z.w);
+          const float ga = fminf(fminf(a0, a1), fminf(a2, a3)), gb = fminf(fminf(b0, b1), fminf(b2, b3));
+          if (ga < best0) { best0 = ga; g0 = j; }
+          if (gb < best1) { best1 = gb; g1 = j; }
         }
-        a.nn_dist[s0 + i] = best; a.nn_idx[s0 + i] = bi;
+        if (g0 >= 0) { a.nn_dist[s0 + i] = best0; a.nn_idx[s0 + i] = tb + first_equal(p0, tx, ty, tz, g0, best0); }
+        if (g1 >= 0) { a.nn_dist[s0 + i1] = best1; a.nn_idx[s0 + i1] = tb + first_equal(p1, tx, ty, tz, g1, best1); }
       }
     }
     // ---- sums of M'M and M'Z (graphSlamTools.cpp:150-171), float products widened to double
