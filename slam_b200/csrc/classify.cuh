@@ -39,7 +39,7 @@ constexpr size_t kKeySmemBytes = (size_t)kWordsPerCloud * 4 + 4 * ssort::kDigits
 __global__ void __launch_bounds__(kKeyThreads, 1) classify_key_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ off,
                                                                       ssort::Plan plan, uint32_t* __restrict__ keys,
                                                                       uint32_t* __restrict__ bitmap, uint32_t* __restrict__ hist,
-                                                                      int32_t* __restrict__ out_count) {
+                                                                      uint32_t* __restrict__ part, int32_t* __restrict__ out_count) {
   extern __shared__ __align__(16) uint32_t key_smem[];
   uint32_t* sbm = key_smem;                                    // [kWordsPerCloud]
   uint32_t* h = key_smem + kWordsPerCloud;                     // [4][kDigits]: two tiles in flight, double buffered
@@ -86,8 +86,8 @@ __global__ void __launch_bounds__(kKeyThreads, 1) classify_key_kernel(const floa
     }
     __syncthreads();
     if (tid < 2 * ssort::kDigits) {              // write the pair's histograms out, clear them for the pair after next
-      const int tt = t + tid / ssort::kDigits;
-      if (tt < t1) hist[ssort::hist_index(tb, tc, tt, tid % ssort::kDigits)] = h2[tid];
+      const int tt = t + tid / ssort::kDigits;        // warp-uniform
+      if (tt < t1) ssort::publish_hist(hist, part, ssort::hist_index(tb, tc, tt, tid % ssort::kDigits), h2[tid]);
       h2[tid] = 0;
     }
   }
@@ -151,21 +151,24 @@ inline int run(const float* d_xyz, const int32_t* d_off, int n_clouds, int64_t n
   if (n <= 0) return 0;
   const ssort::Plan plan{s.tile_base, s.tile_seg, s.group_base, n_clouds};
   const int tiles = ssort::max_tiles(n, n_clouds);
+  uint32_t* part[3];
+  for (int k = 0; k < 3; k++) part[k] = ssort::part_of(s.hist, n, n_clouds, k);
+  cudaMemsetAsync(part[0], 0, 3 * ssort::part_words(n, n_clouds) * 4, st);
   ssort::plan_kernel<<<1, 1024, 0, st>>>(d_off, plan);
   cudaFuncSetAttribute(classify_key_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kKeySmemBytes);   // per device
   classify_key_kernel<<<ssort::max_groups(n, n_clouds), kKeyThreads, kKeySmemBytes, st>>>(d_xyz, d_off, plan, s.keys, s.bitmap, s.hist,
-                                                                                         d_out_count);
+                                                                                         part[0], d_out_count);
   launches += 2;
   // pass 0 (bits 0-6): values implicit; pass 1 (7-13); pass 2 (14-20) emits
-  ssort::scan_table(s.hist, plan, n, st, &launches);
+  ssort::scan_table(s.hist, part[0], plan, n, st, &launches);
   ssort::seg_scatter<true, ssort::StorePairs><<<tiles, ssort::kThreads, 0, st>>>(s.keys, nullptr, d_off, plan, 0, s.hist,
                                                                                  ssort::StorePairs{s.keys_tmp, s.vals_tmp});
-  ssort::seg_hist<<<tiles, ssort::kThreads, 0, st>>>(s.keys_tmp, d_off, plan, ssort::kBits, s.hist);
-  ssort::scan_table(s.hist, plan, n, st, &launches);
+  ssort::seg_hist<<<tiles, ssort::kThreads, 0, st>>>(s.keys_tmp, d_off, plan, ssort::kBits, s.hist, part[1]);
+  ssort::scan_table(s.hist, part[1], plan, n, st, &launches);
   ssort::seg_scatter<false, ssort::StorePairs><<<tiles, ssort::kThreads, 0, st>>>(s.keys_tmp, s.vals_tmp, d_off, plan, ssort::kBits,
                                                                                   s.hist, ssort::StorePairs{s.keys, s.vals});
-  ssort::seg_hist<<<tiles, ssort::kThreads, 0, st>>>(s.keys, d_off, plan, 2 * ssort::kBits, s.hist);
-  ssort::scan_table(s.hist, plan, n, st, &launches);
+  ssort::seg_hist<<<tiles, ssort::kThreads, 0, st>>>(s.keys, d_off, plan, 2 * ssort::kBits, s.hist, part[2]);
+  ssort::scan_table(s.hist, part[2], plan, n, st, &launches);
   ssort::seg_scatter<false, EmitPoint><<<tiles, ssort::kThreads, 0, st>>>(
       s.keys, s.vals, d_off, plan, 2 * ssort::kBits, s.hist, EmitPoint{d_xyz, d_off, s.bitmap, d_out_xyz, d_out_ga, d_out_src});
   launches += 5;

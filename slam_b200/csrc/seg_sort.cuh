@@ -7,7 +7,7 @@
 // (segment, digit, tile-in-segment) so that ONE exclusive scan over the whole table yields global positions.
 // 7 bits per pass (three passes for the 21-bit bin index).  Per pass:
 //   seg_hist     per-tile digit histogram                       (pass 0: produced by the caller's key kernel)
-//   scan_*       exclusive scan of the table (chunk totals, scan of totals, per-chunk scan)
+//   scan_table   exclusive scan of the table, one kernel (the producers publish per-chunk totals with their counts)
 //   seg_scatter  ranks the tile's elements (ballot peer masks inside a warp + per-warp digit counters, warp w owns the
 //                w-th contiguous 512 elements so the counters need no block barrier between rounds), sorts the tile
 //                in shared memory and writes runs of equal digits to consecutive addresses.  The last pass hands
@@ -40,12 +40,23 @@ constexpr int kGroupTiles = 32;
 __host__ __device__ inline int max_tiles(int64_t n, int n_seg) { return (int)(n / kTile) + n_seg; }
 __host__ __device__ inline int max_groups(int64_t n, int n_seg) { return max_tiles(n, n_seg) / kGroupTiles + n_seg; }
 constexpr int kScanChunk = 1024 * 8;            // table entries per scan CTA: 1024 threads x 8
-__host__ __device__ inline size_t hist_words(int64_t n, int n_seg) {
-  const size_t m = (size_t)kDigits * max_tiles(n, n_seg);
-  return m + (m + kScanChunk - 1) / kScanChunk + 16;
-}
+constexpr int kMaxPasses = 4;                   // chunk-total arrays behind the table, one per pass of a sort
+__host__ __device__ inline size_t table_words(int64_t n, int n_seg) { return (size_t)kDigits * max_tiles(n, n_seg); }
+__host__ __device__ inline size_t part_words(int64_t n, int n_seg) { return (table_words(n, n_seg) + kScanChunk - 1) / kScanChunk + 4; }
+__host__ __device__ inline size_t hist_words(int64_t n, int n_seg) { return table_words(n, n_seg) + kMaxPasses * part_words(n, n_seg); }
+// chunk totals of pass `pass` (zeroed by the caller before the first producer runs)
+inline uint32_t* part_of(uint32_t* hist, int64_t n, int n_seg, int pass) { return hist + table_words(n, n_seg) + (size_t)pass * part_words(n, n_seg); }
 __device__ __forceinline__ size_t hist_index(int tb, int tc, int t, int d) {
   return (size_t)kDigits * tb + (size_t)d * tc + t;
+}
+// A producer's warp publishes 32 table entries and adds them to the totals of their scan chunks (one atomic per
+// distinct chunk of the warp), so that the scan needs no reduce pass.  All 32 lanes must call.
+__device__ __forceinline__ void publish_hist(uint32_t* __restrict__ hist, uint32_t* __restrict__ part, size_t idx, uint32_t count) {
+  hist[idx] = count;
+  const uint32_t chunk = (uint32_t)(idx / kScanChunk);
+  const uint32_t peers = __match_any_sync(0xffffffffu, chunk);
+  const uint32_t sum = __reduce_add_sync(peers, count);
+  if ((int)(threadIdx.x & 31) == __ffs(peers) - 1 && sum) atomicAdd(&part[chunk], sum);
 }
 
 __device__ __forceinline__ uint32_t block_excl_scan_1024(uint32_t sum, uint32_t* wsum, uint32_t& total) {
@@ -119,7 +130,7 @@ __device__ __forceinline__ bool locate_tile(const Plan& p, const int32_t* __rest
 }
 
 __global__ void __launch_bounds__(kThreads) seg_hist(const uint32_t* __restrict__ keys, const int32_t* __restrict__ off,
-                                                     Plan p, int shift, uint32_t* __restrict__ hist) {
+                                                     Plan p, int shift, uint32_t* __restrict__ hist, uint32_t* __restrict__ part) {
   __shared__ uint32_t h[kDigits];
   TileRef r;
   if (!locate_tile(p, off, r)) return;
@@ -136,65 +147,34 @@ __global__ void __launch_bounds__(kThreads) seg_hist(const uint32_t* __restrict_
   for (int i = 0; i < kItems; i++)
     if (i * kThreads + tid < r.count) atomicAdd(&h[(k[i] >> shift) & (kDigits - 1)], 1u);
   __syncthreads();
-  if (tid < kDigits) hist[hist_index(r.tb, r.tc, r.t, tid)] = h[tid];
+  if (tid < kDigits) publish_hist(hist, part, hist_index(r.tb, r.tc, r.t, tid), h[tid]);
 }
 
-// ---- exclusive scan of the first kDigits * (number of tiles) table entries, in place, three small kernels
+// ---- exclusive scan of the first kDigits * (number of tiles) table entries, in place: one kernel, every CTA adds up the
+// totals of the chunks before its own (published by the producers) and scans its chunk of 8192 entries
 __device__ __forceinline__ int64_t table_len(const Plan& p) { return (int64_t)kDigits * p.tile_base[p.n_seg]; }
 
-__global__ void __launch_bounds__(1024) scan_reduce(const uint32_t* __restrict__ a, Plan p, uint32_t* __restrict__ part) {
-  __shared__ uint32_t wsum[33];
-  const int64_t m = table_len(p);
-  const int64_t i0 = (int64_t)blockIdx.x * kScanChunk + (int64_t)threadIdx.x * 8;
-  if ((int64_t)blockIdx.x * kScanChunk >= m) return;
-  uint32_t sum = 0;
-#pragma unroll
-  for (int k = 0; k < 8; k++) sum += (i0 + k < m) ? a[i0 + k] : 0u;
-  uint32_t total;
-  block_excl_scan_1024(sum, wsum, total);
-  if (threadIdx.x == 0) part[blockIdx.x] = total;
-}
-
-// one CTA: exclusive scan of the chunk totals (any count, 1024 x 8 at a time)
-__global__ void __launch_bounds__(1024) scan_top(uint32_t* __restrict__ part, Plan p) {
-  __shared__ uint32_t wsum[33];
-  const int64_t np = (table_len(p) + kScanChunk - 1) / kScanChunk;
-  uint32_t carry = 0;
-  for (int64_t base = 0; base < np; base += kScanChunk) {
-    uint32_t v[8], sum = 0;
-    const int64_t i0 = base + (int64_t)threadIdx.x * 8;
-#pragma unroll
-    for (int k = 0; k < 8; k++) { v[k] = (i0 + k < np) ? part[i0 + k] : 0u; sum += v[k]; }
-    uint32_t total;
-    uint32_t run = carry + block_excl_scan_1024(sum, wsum, total);
-#pragma unroll
-    for (int k = 0; k < 8; k++) { if (i0 + k < np) part[i0 + k] = run; run += v[k]; }
-    carry += total;
-  }
-}
-
-__global__ void __launch_bounds__(1024) scan_apply(uint32_t* __restrict__ a, Plan p, const uint32_t* __restrict__ part) {
+__global__ void __launch_bounds__(1024) scan_table_kernel(uint32_t* __restrict__ a, Plan p, const uint32_t* __restrict__ part) {
   __shared__ uint32_t wsum[33];
   const int64_t m = table_len(p);
   if ((int64_t)blockIdx.x * kScanChunk >= m) return;
+  uint32_t pre = 0, before;
+  for (int c = threadIdx.x; c < (int)blockIdx.x; c += 1024) pre += part[c];
+  block_excl_scan_1024(pre, wsum, before);
   const int64_t i0 = (int64_t)blockIdx.x * kScanChunk + (int64_t)threadIdx.x * 8;
   uint32_t v[8], sum = 0;
 #pragma unroll
   for (int k = 0; k < 8; k++) { v[k] = (i0 + k < m) ? a[i0 + k] : 0u; sum += v[k]; }
   uint32_t total;
-  uint32_t run = part[blockIdx.x] + block_excl_scan_1024(sum, wsum, total);
+  uint32_t run = before + block_excl_scan_1024(sum, wsum, total);
 #pragma unroll
   for (int k = 0; k < 8; k++) { if (i0 + k < m) a[i0 + k] = run; run += v[k]; }
 }
 
-inline void scan_table(uint32_t* hist, const Plan& p, int64_t n, cudaStream_t st, int* launches) {
-  const int64_t m = (int64_t)kDigits * max_tiles(n, p.n_seg);
-  const int chunks = (int)((m + kScanChunk - 1) / kScanChunk);
-  uint32_t* part = hist + m;                     // chunk totals live behind the table
-  scan_reduce<<<chunks, 1024, 0, st>>>(hist, p, part);
-  scan_top<<<1, 1024, 0, st>>>(part, p);
-  scan_apply<<<chunks, 1024, 0, st>>>(hist, p, part);
-  if (launches) *launches += 3;
+inline void scan_table(uint32_t* hist, const uint32_t* part, const Plan& p, int64_t n, cudaStream_t st, int* launches) {
+  const int64_t m = (int64_t)table_words(n, p.n_seg);
+  scan_table_kernel<<<(int)((m + kScanChunk - 1) / kScanChunk), 1024, 0, st>>>(hist, p, part);
+  if (launches) *launches += 1;
 }
 
 // Consumers of a scatter pass are split in fetch (loads only) and commit (stores only) so that the loads of a batch of
