@@ -212,7 +212,8 @@ __global__ void __launch_bounds__(kThreads, 4) seg_scatter(const uint32_t* __res
   }
   __syncthreads();
   // Rank inside the warp's span.  The peer mask (lanes of this round with the same digit) is built from one ballot per
-  // digit bit -- MATCH.ANY has a latency of several hundred cycles here and the ballots of eight rounds pipeline.
+  // digit bit -- MATCH.ANY has a latency of several hundred cycles here and the ballots of eight rounds pipeline
+  // (eight pipelined MATCH.ANY per half were measured too: 0.73 ms per classification instead of 0.69).
   uint32_t rank2[kItems / 2];                    // two 16-bit ranks per register
   const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
