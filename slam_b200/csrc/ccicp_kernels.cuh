@@ -41,6 +41,10 @@ constexpr int kThreadsL2 = CCICP_L2_THREADS;
 #define CCICP_CAND_UNROLL 2
 #endif
 constexpr int kCandUnroll = CCICP_CAND_UNROLL;   // candidate loop of nn_search
+#ifndef CCICP_CAND_UNROLL_DENSE
+#define CCICP_CAND_UNROLL_DENSE 4
+#endif
+constexpr int kCandUnrollDense = CCICP_CAND_UNROLL_DENSE;   // L2 variant: the candidates come from global memory, more loads in flight
 constexpr int kRedStride = 10;     // doubles per warp in the reduction scratch (8 sums + 2 ints)
 constexpr unsigned kNoSlot = 0xFFFFu;
 
@@ -256,7 +260,7 @@ __device__ __forceinline__ void nn_search(const float2* mpts, const uint16_t* cs
         const int o1 = j1 - n0, o2 = j2 - n01;
 #if CCICP_TWO_RANGE
         if (n01 == tot) {                     // at most two rows hold candidates: one select less per candidate
-#pragma unroll kCandUnroll
+#pragma unroll (kDense ? kCandUnrollDense : kCandUnroll)
           for (int t = 0; t < tot; t++) {
             const int j = t + (t < n0 ? j0 : o1);
             const float2 p = mpts[j];
@@ -269,7 +273,7 @@ __device__ __forceinline__ void nn_search(const float2* mpts, const uint16_t* cs
           continue;
         }
 #endif
-#pragma unroll kCandUnroll
+#pragma unroll (kDense ? kCandUnrollDense : kCandUnroll)
         for (int t = 0; t < tot; t++) {
           int off = o2;
           off = t < n01 ? o1 : off;
