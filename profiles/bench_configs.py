@@ -47,7 +47,8 @@ def main():
         run(ctx, "C2 default mode (pinned)", b2, prm)
         run(ctx, "C2 CCICP_F_EXACT_SUMS (pinned)", b2, capi.fixed_iter_params(30, flags=capi.F_EXACT_SUMS))
     if "c3" in which:
-        run(ctx, "C3 loop-closure 1081-beam", scangen.generate(10**6, pairs or 16384, config=3), prm)
+        run(ctx, "C3 loop-closure 1081-beam (pinned host buffers, chunked pipeline)",
+            scangen.generate(10**6, pairs or 16384, config=3, pinned=capi.pinned_array), prm)
     if "c4" in which:
         run(ctx, "C4 dense 32768-point", scangen.generate(5000, pairs or 148, config=4), prm, reps=2)
     if "c5" in which:

@@ -22,6 +22,7 @@ struct DevBuf {
 };
 
 struct ccicp_ctx {
+  DevBuf h_init, h_out;       // pinned staging for the small per-pair arrays when the caller's are pageable
   int device = 0;
   int sm_count = 0;
   int max_smem_optin = 0;
@@ -65,6 +66,23 @@ int reserve(ccicp_ctx* ctx, DevBuf& b, size_t bytes) {
   if (e != cudaSuccess) { b.p = nullptr; return fail_cuda(ctx, e, "cudaMalloc"); }
   b.cap = want;
   return CCICP_OK;
+}
+
+int reserve_pinned(ccicp_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return CCICP_OK;
+  if (b.p) { cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMallocHost(&b.p, want);
+  if (e != cudaSuccess) { b.p = nullptr; return fail_cuda(ctx, e, "cudaMallocHost"); }
+  b.cap = want;
+  return CCICP_OK;
+}
+
+// true when an asynchronous copy from / to this host pointer does not block the calling thread
+bool is_pinned(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
 }
 
 int round_up(int x, int m) { return (x + m - 1) / m * m; }
@@ -273,6 +291,8 @@ int ccicp_destroy(ccicp_ctx* ctx) {
                     &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
                     &ctx->l_dist, &ctx->l_idx, &ctx->l_info, &ctx->l_num, &ctx->l_status};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
+  if (ctx->h_init.p) cudaFreeHost(ctx->h_init.p);
+  if (ctx->h_out.p) cudaFreeHost(ctx->h_out.p);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->chunk_ev) if (ev) cudaEventDestroy(ev);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -379,6 +399,21 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
     for (int c = 1; c <= rest; c++) bound[n_chunks + c] = pos + (int32_t)((int64_t)(n_pairs - pos) * c / rest);
     n_chunks += rest;
   }
+  // A pageable `out` would make every chunk's record copy wait on the host for that chunk's kernel (and a pageable
+  // init array every chunk's upload), which serialises the pipeline: those two small arrays go through pinned staging.
+  const double* init_src = init_Rt;
+  ccicp_result* out_dst = out;
+  if (n_chunks > 1) {
+    if (!is_pinned(init_Rt)) {
+      if ((rc = reserve_pinned(ctx, ctx->h_init, n_prob * 48))) return rc;
+      memcpy(ctx->h_init.p, init_Rt, n_prob * 48);
+      init_src = (const double*)ctx->h_init.p;
+    }
+    if (!is_pinned(out)) {
+      if ((rc = reserve_pinned(ctx, ctx->h_out, n_out * sizeof(ccicp_result)))) return rc;
+      out_dst = (ccicp_result*)ctx->h_out.p;
+    }
+  }
   cudaStream_t cs = ctx->copy_stream;
   CK(cudaEventRecord(ctx->ev[0], cs));
   CK(cudaMemcpyAsync(ctx->d_moff.p, model_off, off_bytes, cudaMemcpyHostToDevice, cs));
@@ -389,7 +424,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
     const int64_t s0 = scene_off[2 * (size_t)p0], s1 = scene_off[2 * (size_t)p1];
     if (m1 > m0) CK(cudaMemcpyAsync((char*)ctx->d_model.p + m0 * 16, model_xy + 2 * m0, (size_t)(m1 - m0) * 16, cudaMemcpyHostToDevice, cs));
     if (s1 > s0) CK(cudaMemcpyAsync((char*)ctx->d_scene.p + s0 * 16, scene_xy + 2 * s0, (size_t)(s1 - s0) * 16, cudaMemcpyHostToDevice, cs));
-    CK(cudaMemcpyAsync((char*)ctx->d_init.p + (size_t)p0 * n_seeds * 48, init_Rt + (size_t)p0 * n_seeds * 6,
+    CK(cudaMemcpyAsync((char*)ctx->d_init.p + (size_t)p0 * n_seeds * 48, init_src + (size_t)p0 * n_seeds * 6,
                        (size_t)(p1 - p0) * n_seeds * 48, cudaMemcpyHostToDevice, cs));
     CK(cudaEventRecord(ctx->chunk_ev[c], cs));
     if (c == n_chunks - 1) CK(cudaEventRecord(ctx->ev[1], cs));
@@ -402,7 +437,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
     if (rc) { cudaDeviceSynchronize(); return rc; }
     if (c == n_chunks - 1) CK(cudaEventRecord(ctx->ev[4], ks));
     const size_t o0 = best_of ? (size_t)p0 : (size_t)p0 * n_seeds, o1 = best_of ? (size_t)p1 : (size_t)p1 * n_seeds;
-    CK(cudaMemcpyAsync(out + o0, (char*)ctx->d_out.p + o0 * sizeof(ccicp_result), (o1 - o0) * sizeof(ccicp_result),
+    CK(cudaMemcpyAsync(out_dst + o0, (char*)ctx->d_out.p + o0 * sizeof(ccicp_result), (o1 - o0) * sizeof(ccicp_result),
                        cudaMemcpyDeviceToHost, ks));
     if (c == n_chunks - 1) {
       if (corr_idx && n_scene) CK(cudaMemcpyAsync(corr_idx, ctx->d_corr.p, (size_t)n_scene * n_seeds * 4, cudaMemcpyDeviceToHost, ks));
@@ -412,6 +447,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   CK(cudaStreamSynchronize(cs));
   if (n_chunks == 1) CK(cudaStreamSynchronize(st));
   else { for (auto& ks : ctx->kstream) CK(cudaStreamSynchronize(ks)); }
+  if (out_dst != out) memcpy(out, out_dst, n_out * sizeof(ccicp_result));
   ctx->timed_copies = true;
   return CCICP_OK;
 }
