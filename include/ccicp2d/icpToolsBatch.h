@@ -17,6 +17,8 @@
 #define CCICP2D_B200_ICP_TOOLS_BATCH_H
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "ccicp2d_b200.h"
@@ -24,6 +26,44 @@
 #ifndef ICP_MAX_PTS
 #define ICP_MAX_PTS 20000      // ccicp2d/include/ccicp2d/icpTools.h:21
 #endif
+
+// Growable array of doubles in page-locked host memory (ccicp_host_alloc): the packed scan coordinates are what the
+// batch call uploads chunk by chunk under the running kernels, which only overlaps from pinned memory.  Falls back to
+// malloc when pinned memory is not available.
+class CCICPPinnedDoubles {
+ public:
+  CCICPPinnedDoubles() : p_(nullptr), n_(0), cap_(0), pinned_(false) {}
+  ~CCICPPinnedDoubles() { release(); }
+  CCICPPinnedDoubles(const CCICPPinnedDoubles&) = delete;
+  CCICPPinnedDoubles& operator=(const CCICPPinnedDoubles&) = delete;
+  void clear() { n_ = 0; }
+  size_t size() const { return n_; }
+  const double* data() const { return p_; }
+  void push2(double a, double b) {
+    if (n_ + 2 > cap_) grow(n_ + 2);
+    p_[n_++] = a; p_[n_++] = b;
+  }
+
+ private:
+  void grow(size_t need) {
+    size_t cap = cap_ ? 2 * cap_ : 4096;
+    while (cap < need) cap *= 2;
+    void* q = nullptr;
+    bool pinned = ccicp_host_alloc(&q, cap * sizeof(double)) == CCICP_OK && q;
+    if (!pinned) q = std::malloc(cap * sizeof(double));
+    if (!q) { std::fprintf(stderr, "CCICPBatch: out of host memory\n"); std::abort(); }
+    if (n_) std::memcpy(q, p_, n_ * sizeof(double));
+    release();
+    p_ = (double*)q; cap_ = cap; pinned_ = pinned;
+  }
+  void release() {
+    if (p_) { if (pinned_) ccicp_host_free(p_); else std::free(p_); }
+    p_ = nullptr; cap_ = 0;
+  }
+  double* p_;
+  size_t n_, cap_;
+  bool pinned_;
+};
 
 class CCICPBatch {
  public:
@@ -100,16 +140,16 @@ class CCICPBatch {
 
  private:
   template <class Pts>
-  static void append(const Pts& pts, std::vector<double>& xy, std::vector<int32_t>& off) {
+  static void append(const Pts& pts, CCICPPinnedDoubles& xy, std::vector<int32_t>& off) {
     const size_t n = pts.size();
-    for (size_t i = 0; i < n; i++) { xy.push_back(pts[i](0)); xy.push_back(pts[i](1)); }
+    for (size_t i = 0; i < n; i++) xy.push2(pts[i](0), pts[i](1));
     off.push_back(off.back() + (int32_t)n);
   }
 
   ccicp_ctx* ctx_;
   int status_;
   ccicp_params prm_;
-  std::vector<double> model_xy_, scene_xy_;
+  CCICPPinnedDoubles model_xy_, scene_xy_;
   std::vector<int32_t> model_off_, scene_off_;
   std::vector<ccicp_pose> init_, out_;
   std::vector<ccicp_result> rec_;
