@@ -41,6 +41,13 @@ constexpr int kThreadsL2 = CCICP_L2_THREADS;
 #define CCICP_CAND_UNROLL 2
 #endif
 constexpr int kCandUnroll = CCICP_CAND_UNROLL;   // candidate loop of nn_search
+#ifndef CCICP_ROW_LOOPS
+#define CCICP_ROW_LOOPS 1
+#endif
+#ifndef CCICP_ROW_UNROLL
+#define CCICP_ROW_UNROLL 4
+#endif
+constexpr int kRowUnroll = CCICP_ROW_UNROLL;
 #ifndef CCICP_CAND_UNROLL_DENSE
 #define CCICP_CAND_UNROLL_DENSE 4
 #endif
@@ -258,6 +265,24 @@ __device__ __forceinline__ void nn_search(const float2* mpts, const uint16_t* cs
         if (y + 2 <= yb) { j2 = r0[2 * G + xs]; e2 = r0[2 * G + xe + 1]; }
         const int n0 = e0 - j0, n01 = n0 + (e1 - j1), tot = n01 + (e2 - j2);
         const int o1 = j1 - n0, o2 = j2 - n01;
+        // On chip: one plain loop per row -- no index mapping (13 instead of 18.5 instructions per candidate) but three
+        // trip counts per warp (+22 % trips): +3.5 % on C2.  The L2 variant keeps the flat loop over the three ranges (all
+        // lanes of a warp run the same number of trips, more loads in flight): row loops cost it 13 %.
+        if constexpr (CCICP_ROW_LOOPS && !kDense) {
+          const int jb[3] = {j0, j1, j2}, je[3] = {e0, e1, e2};
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+#pragma unroll kRowUnroll
+            for (int j = jb[k]; j < je[k]; j++) {
+              const float2 p = mpts[j];
+              const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+              const float d = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+              bslot = d < best ? j : bslot;
+              second = fminf(second, fmaxf(d, best));
+              best = fminf(best, d);
+            }
+          }
+        } else {
 #if CCICP_TWO_RANGE
         if (n01 == tot) {                     // at most two rows hold candidates: one select less per candidate
 #pragma unroll (kDense ? kCandUnrollDense : kCandUnroll)
@@ -285,6 +310,7 @@ __device__ __forceinline__ void nn_search(const float2* mpts, const uint16_t* cs
           bslot = d < best ? j : bslot;
           second = fminf(second, fmaxf(d, best));
           best = fminf(best, d);
+        }
         }
       }
     }
