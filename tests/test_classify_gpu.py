@@ -75,3 +75,20 @@ def test_device_api_gather_paths(ctx):
 def test_one_large_cloud_spans_several_tile_groups(ctx):
     """> 32 tiles: the key kernel splits the cloud over several CTAs that merge their bitmaps with atomics."""
     _device_call(ctx, [synthetic_cloud(11, 300000), synthetic_cloud(12, 50)], 0)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_fuzz_ragged_batches(ctx, seed):
+    """Random cloud counts and sizes around the tile (4096) and tile-group (32 tiles) boundaries, clustered points (many
+    per bin), points outside the grid and NaNs."""
+    rng = np.random.default_rng(1234 + seed)
+    sizes = [int(s) for s in rng.choice([0, 1, 2, 31, 4095, 4096, 4097, 8192, 10000, 131072, 131073, 20000], size=rng.integers(3, 9))]
+    clouds = []
+    for k, n in enumerate(sizes):
+        c = synthetic_cloud(1000 * seed + k, max(n, 16))[:n]
+        if n > 100:
+            c[rng.integers(0, n, n // 50), 0] = np.nan                   # dropped by the bin test
+            c[rng.integers(0, n, n // 20)] = c[rng.integers(0, n)]       # duplicates: long runs inside one bin
+            c[rng.integers(0, n, n // 50), :2] *= 100.0                   # far outside the 600 m grid
+        clouds.append(np.ascontiguousarray(c))
+    _device_call(ctx, clouds, 0)
