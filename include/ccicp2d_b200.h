@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CCICP_ABI_VERSION 2
+#define CCICP_ABI_VERSION 3
 
 /* ---- call-level error codes ------------------------------------------- */
 enum {
@@ -75,6 +75,9 @@ enum {
   CCICP_F_FIRST_BELOW    = 1u << 5, /* with BEST_OF_SEEDS: global_matching's acceptance rule (global_match.cpp:131-151) -- the
                                        FIRST seed (lowest index) whose normalised score  score / n_scene  is below
                                        score_threshold wins, instead of the arg-min                                            */
+  CCICP_F_TRIM           = 1u << 6, /* north_star extra, NO counterpart in the reference (its only outlier test is the fixed
+                                       gate, icpPointToPoint.cpp:76,111): trimmed rejection, keep the params.trim_frac
+                                       fraction of the gated correspondences per iteration.  Off in every parity run. */
   CCICP_F_NO_TIE_REPLAY  = 1u << 3, /* diagnostics only: skip the kd-tree tie replay (ties -> lowest grid slot)                 */
   CCICP_F_EXACT_SUMS     = 1u << 4  /* evaluate centroids, H, the SVD (Matrix::svd, matrix.cpp:582-810) and the compose step in
                                        the reference's own sequential order: R,t of every iteration are then BIT-IDENTICAL to
@@ -95,6 +98,8 @@ typedef struct ccicp_params {
                              (DIST_MOVE_THRESH 10 m) ...                                            */
   double   reject_rot;    /* ... or the wrapped |dyaw| exceeds this (ROT_MOVE_THRESH 0.2 rad)
                              (graph_slam/src/graphSlamTools.cpp:332-362, graphSlamTools.h:35-36)    */
+  double   trim_frac;     /* CCICP_F_TRIM: fraction in (0, 1] of each iteration's gated correspondences that is kept
+                             (those with the smallest squared distance); default 1 = the reference's behaviour     */
 } ccicp_params;
 
 /* One record per (pair, seed) problem -- 160 bytes. */

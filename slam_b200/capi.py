@@ -17,13 +17,13 @@ OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
 ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
 ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
 ST_NO_SEED_BELOW, ST_EDGE_REJECTED = 1024, 2048
-F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW = 1, 2, 4, 8, 16, 32
+F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW, F_TRIM = 1, 2, 4, 8, 16, 32, 64
 
 
 class Params(C.Structure):
     _fields_ = [("max_iter", C.c_int32), ("flags", C.c_uint32), ("min_delta", C.c_double),
                 ("indist", C.c_double), ("min_corr_frac", C.c_double), ("score_threshold", C.c_double),
-                ("reject_dist", C.c_double), ("reject_rot", C.c_double)]
+                ("reject_dist", C.c_double), ("reject_rot", C.c_double), ("trim_frac", C.c_double)]
 
 
 class LaunchInfo(C.Structure):
@@ -102,9 +102,9 @@ def default_params(**kw):
     return p
 
 
-def fixed_iter_params(iters=30, flags=0, indist=5.0):
+def fixed_iter_params(iters=30, flags=0, indist=5.0, trim_frac=1.0):
     """BASELINE.json's setting: setMaxIterations(30) + setMinDeltaParam(-2)."""
-    return default_params(max_iter=iters, min_delta=-2.0, flags=flags, indist=indist)
+    return default_params(max_iter=iters, min_delta=-2.0, flags=flags, indist=indist, trim_frac=trim_frac)
 
 
 def _ptr(a):

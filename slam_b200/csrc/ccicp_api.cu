@@ -115,8 +115,10 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   if (a.ccap < 64) a.ccap = 64;
   // on-chip variant when the pair's working set fits the SM's shared memory, else the L2 variant
   const bool exact = (prm->flags & CCICP_F_EXACT_SUMS) != 0;
-  auto k_on = exact ? icp_pair_exact_kernel : icp_pair_kernel;
-  auto k_l2 = exact ? icp_pair_l2_exact_kernel : icp_pair_l2_kernel;
+  const bool trim = (prm->flags & CCICP_F_TRIM) != 0;
+  if (trim && (exact || !(prm->trim_frac > 0.0) || prm->trim_frac > 1.0)) return CCICP_E_INVALID;
+  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : icp_pair_kernel;
+  auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : icp_pair_l2_kernel;
   cudaFuncAttributes fa_on;
   CK(cudaFuncGetAttributes(&fa_on, k_on));
   size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false);
@@ -183,6 +185,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   a.pair_base = pair_base;
   a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
   a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
+  a.trim_frac = prm->trim_frac;
   a.total_scene = total_scene; a.max_model = max_model;
 
   CK(cudaMemsetAsync(a.work_counter, 0, 4, st));
@@ -247,6 +250,7 @@ void ccicp_default_params(ccicp_params* p) {
   p->score_threshold = 0.002;  // MAX_SCORE, global_match.cpp:30
   p->reject_dist = 0.0;        // off; graph_slam uses 10 m / 0.2 rad (graphSlamTools.h:35-36)
   p->reject_rot = 0.0;
+  p->trim_frac = 1.0;          // off (CCICP_F_TRIM is an extra the reference does not have)
 }
 
 int ccicp_create(ccicp_ctx** out, int device) {

@@ -75,6 +75,7 @@ struct IcpArgs {
   int32_t pair_base;             // this launch registers pairs [pair_base, pair_base + n_pairs)
   int32_t max_iter; uint32_t flags;
   double min_delta, indist;
+  double trim_frac;              // CCICP_F_TRIM: fraction of the gated correspondences kept per iteration
   int64_t total_scene;           // corr_idx seed stride (scene points in the whole batch)
   int32_t mcap, scap, ccap;      // shared-memory capacities: model points, scene points, cells
   int32_t max_model;             // scratch sizing

@@ -148,7 +148,74 @@ __device__ __noinline__ void exact_step(const Smem& s, const double* Rt, int ns,
   }
 }
 
-template <int kThreads, bool kGlobal, bool kExact>
+// CCICP_F_TRIM (a north_star extra; the reference has only the fixed gate): keep the `trim_frac` fraction of this
+// iteration's gated correspondences with the smallest squared distances.  The threshold is the k-th smallest distance,
+// k = ceil(trim_frac * n_gated), found by a 4 x 8-bit radix select over the (non-negative, hence order-preserving) float
+// bit patterns in shared memory; correspondences at the threshold distance are all kept.  A trimmed scene point is
+// treated like an ungated one from here on (slot = none: no part in the sums, the indices, the score, the information
+// matrix, and no warm start next iteration).  The distance is recomputed with the search's own float expression.
+template <int kThreads>
+__device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double* Rt, int ns, int tid, uint32_t* th) {
+  auto key_of = [&](int i, unsigned slot) -> uint32_t {
+    const double2 sp = s.scene[i];
+    float qx, qy;
+    transform(Rt, sp.x, sp.y, qx, qy);
+    const float2 p = s.mpts[slot];
+    const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+    return __float_as_uint(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+  };
+  uint32_t prefix = 0, mask = 0;
+  for (int pass = 3; pass >= 0; pass--) {
+    __syncthreads();
+    if (tid < 256) th[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < ns; i += kThreads) {
+      const unsigned slot = s.slots[i];
+      if (slot == kNoSlot) continue;
+      const uint32_t key = key_of(i, slot);
+      if ((key & mask) == prefix) atomicAdd(&th[(key >> (8 * pass)) & 255u], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {
+      uint32_t c[8], sum = 0;
+#pragma unroll
+      for (int q = 0; q < 8; q++) { c[q] = th[tid * 8 + q]; sum += c[q]; }
+      uint32_t incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += t; }
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      uint32_t k = th[257];
+      if (pass == 3) {                                     // first pass: all gated correspondences are counted
+        const double want = ceil(a.trim_frac * (double)total);
+        k = want < 1.0 ? 1u : (want > (double)total ? total : (uint32_t)want);
+      }
+      const uint32_t excl = incl - sum;
+      if (total > 0 && excl < k && k <= incl) {            // exactly one lane
+        uint32_t run = excl;
+        int dgt = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) { if (run + c[q] < k) { run += c[q]; dgt = q + 1; } else break; }
+        th[256] = (uint32_t)(tid * 8 + dgt);
+        th[257] = k - run;                                 // rank inside the chosen digit
+      }
+      if (tid == 0) th[258] = total;
+    }
+    __syncthreads();
+    if (th[258] == 0) return;                              // nothing gated: nothing to trim (uniform)
+    prefix |= th[256] << (8 * pass);
+    mask |= 0xFFu << (8 * pass);
+  }
+  for (int i = tid; i < ns; i += kThreads) {
+    const unsigned slot = s.slots[i];
+    if (slot == kNoSlot) continue;
+    if (key_of(i, slot) > prefix) {
+      s.slots[i] = (uint16_t)kNoSlot;
+      atomicAnd(&s.tiebits[i >> 5], ~(1u << (i & 31)));
+    }
+  }
+}
+
+template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
@@ -157,6 +224,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   __shared__ double exact_s[kExact ? 16 : 1];
   __shared__ GridP grid_s[2];
   __shared__ int misc_s[16];
+  __shared__ uint32_t trim_s[kTrim ? 260 : 1];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
   Smem s = carve<kGlobal>(base, a.mcap, a.scap, a.ccap, red_s, rtprev_s, grid_s, misc_s);
   const int tid = threadIdx.x;
@@ -235,6 +303,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             }
             s.slots[i] = (uint16_t)slot;
           }
+          if constexpr (kTrim) trim_select<kThreads>(a, s, Rt, ns, tid, trim_s);
           double v[8];
           int cnt;
           sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);        // loop B: converged accumulation
@@ -330,6 +399,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             }
             s.slots[i] = (uint16_t)slot;
           }
+          if constexpr (kTrim) trim_select<kThreads>(a, s, P, ns, tid, trim_s);
         }
         const bool want_info = (a.flags & CCICP_F_INFO) != 0;
         const bool fixed_dy = (a.flags & CCICP_F_INFO_FIXED_DY) != 0;
@@ -414,6 +484,13 @@ __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_exa
 }
 __global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_exact_kernel(const IcpArgs a) {
   icp_pair_body<kThreadsL2, true, true>(a);
+}
+// CCICP_F_TRIM instantiations (north_star extra: trimmed outlier rejection)
+__global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_trim_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsOnChip, false, false, true>(a);
+}
+__global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_trim_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsL2, true, false, true>(a);
 }
 
 // best-of-seeds: one warp per pair.  Default: arg-min of score over seeds with num_corr >= min_corr_frac * n_scene,
