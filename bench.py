@@ -36,6 +36,29 @@ PAIRS_PER_GPU = 4096
 ITERS = 30
 INDIST = 5.0
 SEED0 = 1000                      # seeds 1000...
+C3_SEED0 = 1000000                # seeds 10^6..., offsets +-2 m / +-0.3 rad, init = truth + noise
+C3_TOTAL = 262144                 # loop-closure candidates of the whole job (strong scaling: C3_TOTAL / N per GPU)
+
+
+def generate_chunked(seed_lo, n_pairs, config, pinned, chunk=16384):
+    """scangen.generate in chunks (its dense [pairs, beams, 2] temporaries stay small), packed into one pinned CSR."""
+    from slam_b200 import scangen
+    if n_pairs <= chunk:
+        return scangen.generate(seed_lo, n_pairs, config=config, pinned=pinned)
+    parts = [scangen.generate(seed_lo + lo, min(chunk, n_pairs - lo), config=config) for lo in range(0, n_pairs, chunk)]
+    def cat(xy_name, off_name):
+        xy = pinned((sum(len(getattr(b, xy_name)) for b in parts), 2), np.float64)
+        off, o = [np.zeros(1, np.int32)], 0
+        for b in parts:
+            a = getattr(b, xy_name)
+            xy[o:o + len(a)] = a
+            off.append(getattr(b, off_name)[1:] + np.int32(o))
+            o += len(a)
+        return xy, np.concatenate(off).astype(np.int32)
+    mxy, moff = cat("model_xy", "model_off")
+    sxy, soff = cat("scene_xy", "scene_off")
+    return scangen.Batch(mxy, moff, sxy, soff, np.concatenate([b.truth for b in parts]),
+                         np.concatenate([b.init for b in parts]), np.concatenate([b.seeds for b in parts]))
 
 
 def algorithmic_bytes(batch, result_bytes=160):
@@ -79,7 +102,7 @@ def cpu_reference_rate(batch, cores, pairs_per_core, reps=1):
         wall = time.perf_counter() - t0
     n = sum(o[0] for o in out)
     return dict(value=n / wall, unit=UNIT, cores=cores, kind="reference" if kind == "reference" else "port",
-                sample="%d pairs x %d rep(s) on each of %d processes (first pairs of the same C2 batch), %.1f s wall"
+                sample="%d pairs x %d rep(s) on each of %d processes (first pairs of the same batch), %.1f s wall"
                        % (pairs_per_core, reps, cores, wall)), wall
 
 
@@ -178,10 +201,15 @@ def gpu_arm(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    n_pairs = args.pairs
-    seed_lo, n_local = sharding.shard_seeds(SEED0, n_pairs * world, rank, world)     # contiguous pair ranges
-    assert n_local == n_pairs
-    batch = scangen.generate(seed_lo, n_pairs, config=1, pinned=capi.pinned_array)
+    c3 = args.workload == "c3"
+    if c3:       # the whole loop-closure batch is split over the ranks (strong scaling)
+        seed_lo, n_pairs = sharding.shard_seeds(C3_SEED0, args.total_pairs, rank, world)
+        assert n_pairs * world == args.total_pairs, "--total-pairs must divide by the number of GPUs"
+    else:        # weak scaling: args.pairs per GPU
+        n_pairs = args.pairs
+        seed_lo, n_local = sharding.shard_seeds(SEED0, n_pairs * world, rank, world)     # contiguous pair ranges
+        assert n_local == n_pairs
+    batch = generate_chunked(seed_lo, n_pairs, 3 if c3 else 1, capi.pinned_array)
     init_h = capi.pinned_array((n_pairs, 6), np.float64)
     init_h[:] = batch.init_Rt()
     out_h = capi.pinned_array((n_pairs,), capi.RESULT_DTYPE)
@@ -261,14 +289,23 @@ def gpu_arm(args, rank, world, local_rank):
     k_ms = float(np.mean(kernel_ms))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     traffic = load_traffic()
+    if traffic:      # the committed capture is one launch of `pairs_per_launch` pairs; both figures are linear in the pairs
+        f = n_pairs / float(traffic.get("pairs_per_launch", PAIRS_PER_GPU))
+        for k in ("dram_bytes_per_launch", "warp_instr_per_launch"):
+            if traffic.get(k):
+                traffic[k] = traffic[k] * f
     h2d = int(batch.model_xy.nbytes + batch.scene_xy.nbytes + batch.model_off.nbytes + batch.scene_off.nbytes + init_h.nbytes)
     d2h = int(out_h.nbytes)
     line = {
         "metric": METRIC, "value": world * n_pairs / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32 distances / f64 transform+sums / int32 indices",
+        "scaling": "strong" if c3 else "weak", "vs_baseline": None,
+        "dtype": "f32 distances / f64 transform+sums / int32 indices",
         "data": "synthetic (seeded 1081-beam ray-cast rooms, slam_b200/csrc/scangen.c)",
-        "config": {"workload": "C2: %d odometry scan pairs per GPU, 1081 beams, two classes, %d fixed iterations, indist %g"
+        "config": {"workload": ("C3: %d loop-closure scan pairs in total (%d per GPU), offsets +-2 m / +-0.3 rad, init = truth + "
+                                "N(0.3 m, 0.05 rad), 1081 beams, two classes, %d fixed iterations, indist %g"
+                                % (n_pairs * world, n_pairs, ITERS, INDIST)) if c3 else
+                               "C2: %d odometry scan pairs per GPU, 1081 beams, two classes, %d fixed iterations, indist %g"
                                % (n_pairs, ITERS, INDIST),
                    "pairs_per_gpu": n_pairs, "iters": ITERS, "parallelism": "pairs sharded over %d GPU(s)" % world,
                    "l2": "inputs %.0f MB per GPU > 126 MB L2, no flush" % ((alg_bytes) / 1e6),
@@ -302,6 +339,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="scan pairs per GPU per step")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3"],
+                    help="c2 (default, the metric's configuration): --pairs odometry pairs per GPU, weak scaling; "
+                         "c3: --total-pairs loop-closure candidates split over the GPUs, records gathered over NCCL")
+    ap.add_argument("--total-pairs", type=int, default=C3_TOTAL, help="c3 only: pairs of the whole job")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-pairs-per-core", type=int, default=0)
     args = ap.parse_args()
@@ -315,7 +356,8 @@ def main():
             return 0
         from slam_b200 import scangen
         cores = host_cores()
-        batch = scangen.generate(SEED0, min(args.pairs, max(64, cores * 8)), config=1)
+        c3 = args.workload == "c3"
+        batch = scangen.generate(C3_SEED0 if c3 else SEED0, min(args.pairs, max(64, cores * 8)), config=3 if c3 else 1)
         ppc = args.cpu_pairs_per_core or 48           # ~12 ms each -> ~0.6 s per core per step
         for _ in range(args.warmup):
             cpu_reference_rate(batch, cores, 2)
@@ -329,8 +371,8 @@ def main():
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(walls)) * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64 (CPU)",
                 "data": "synthetic (same generator and seeds as the GPU arm)",
-                "config": {"workload": "C2 sample: %d pairs per core per step, 1081 beams, %d fixed iterations, indist %g"
-                                       % (ppc, ITERS, INDIST), "iters": ITERS},
+                "config": {"workload": "%s sample: %d pairs per core per step, 1081 beams, %d fixed iterations, indist %g"
+                                       % (args.workload.upper(), ppc, ITERS, INDIST), "iters": ITERS},
                 "cpu_baseline": cb,
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line), flush=True)
@@ -341,7 +383,8 @@ def main():
         # before any CUDA initialisation: the workers are forked
         from slam_b200 import scangen
         cores = host_cores()
-        sample = scangen.generate(SEED0, min(args.pairs, 256), config=1)
+        c3 = args.workload == "c3"
+        sample = scangen.generate(C3_SEED0 if c3 else SEED0, min(args.pairs, 256), config=3 if c3 else 1)
         ppc = args.cpu_pairs_per_core or 1000        # ~12.5 ms each -> ~12 s of CPU work per core
         cpu_line, _ = cpu_reference_rate(sample, cores, ppc)
     line = gpu_arm(args, rank, world, local_rank)

@@ -25,5 +25,6 @@ t = {"kernel": d.get('Kernel Name', 'icp_pair_kernel'),
      "issue_active_pct": float(d['smsp__issue_active.avg.pct_of_peak_sustained_active']),
      "gpu_time_ms_under_ncu": float(d['gpu__time_duration.sum']) * {'ms': 1, 'us': 1e-3, 'ns': 1e-6, 'msecond': 1, 'usecond': 1e-3, 'nsecond': 1e-6}.get(u['gpu__time_duration.sum'], 1)}
 t["dram_bytes_per_launch"] = t["dram_bytes_read"] + t["dram_bytes_write"]
+t["pairs_per_launch"] = 4096          # bench.py default (C2); bench.py scales both figures for other batch sizes
 json.dump(t, open(os.path.join(here, 'traffic.json'), 'w'), indent=1)
 print(json.dumps(t))
