@@ -192,8 +192,12 @@ struct SmemPts {
   }
 };
 
-__host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
+__host__ __device__ inline size_t replay_nodes_bytes(int max_model) {
   return align_up((size_t)(2 * max_model + 16) * sizeof(kdreplay::LNode), 16);
+}
+// per CTA: the lazily built tree nodes of both classes + the rank tables of the cooperative (L2 variant) partition
+__host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
+  return replay_nodes_bytes(max_model) + align_up((size_t)(max_model + 16) * sizeof(uint16_t), 16);
 }
 
 // Tied queries are listed in s.tiebits.  Thread c (c = 0 GA, 1 NGA) replays the tied queries of its class one
@@ -244,8 +248,23 @@ template <int kThreads>
 struct CtaCoop {
   int tid, nt;
   float* sv; uint16_t* si; int cap; int* bcast;
+  uint16_t* rank;                     // [>= class size] global scratch: rank tables of the data-parallel partition
   float* fred;                        // [kThreads/32][8] shared
   __device__ __forceinline__ void sync() { __syncthreads(); }
+  // block-wide exclusive prefix sum over tid; the total goes to every thread
+  __device__ __forceinline__ int exscan(int v, int* total) {
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
+    int* wsum = (int*)fred;
+    __syncthreads();
+    if ((tid & 31) == 31) wsum[tid >> 5] = incl;
+    __syncthreads();
+    int woff = 0, tot = 0;
+    for (int w = 0; w < kThreads / 32; w++) { const int c = wsum[w]; woff += w < (tid >> 5) ? c : 0; tot += c; }
+    *total = tot;
+    return woff + incl - v;
+  }
   __device__ __forceinline__ void minmax4(float* lo, float* hi) {
 #pragma unroll
     for (int k = 0; k < 4; k++) {
@@ -270,8 +289,11 @@ struct CtaCoop {
   }
 };
 
+// Inlined on purpose: as an out-of-line call its register footprint decided which of the caller's loop-carried values
+// ptxas kept in local memory for their WHOLE live range -- with the data-parallel partition inside, the no-tie path of
+// the C4 wave went from 17.7 to 22.4 ms; inlined it is 17.4 ms (the cold block is spilled around, not through).
 template <int kThreads>
-__device__ __noinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid,
+__device__ __forceinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid,
                                               char* stage, int stage_cap, float* fred) {
   __syncthreads();
   for (int cls = 0; cls < 2; cls++) {
@@ -285,6 +307,7 @@ __device__ __noinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s, c
     co.tid = tid; co.nt = kThreads; co.cap = stage_cap;
     co.sv = (float*)stage; co.si = (uint16_t*)(stage + (size_t)stage_cap * 4);
     co.bcast = &s.misc[15]; co.fred = fred;
+    co.rank = (uint16_t*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta + replay_nodes_bytes(a.max_model)) + g.first;
     int* nn = &s.misc[M_NNODE + cls];
     int state = s.misc[M_TREE + cls];
     const int i0 = cls ? nsGA : 0, i1 = cls ? ns : nsGA;

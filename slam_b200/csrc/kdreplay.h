@@ -18,9 +18,11 @@
 #if defined(__CUDACC__)
 #define KD_HD __host__ __device__ __forceinline__
 #define KD_FN __host__ __device__
+#define KD_COLD __host__ __device__ __noinline__
 #else
 #define KD_HD inline
 #define KD_FN inline
+#define KD_COLD inline
 #endif
 
 namespace kdreplay {
@@ -402,8 +404,9 @@ KD_FN int lazy_nearest(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n
 // ---------------------------------------------------------------------------------------------------------
 // Cooperative variant (large scans, L2 kernel): every thread of the CTA runs the SAME traversal on the same
 // query (all control flow is uniform); a node split is shared out: the gather of the cut coordinate and the
-// bounding boxes of the children are data-parallel, only the float mean (a sequential sum, kdtree.cpp:181-186)
-// and the in-order partition (kdtree.cpp:294-317) run on one thread, on a staged copy (`sv`, `si`).
+// bounding boxes of the children are data-parallel, and so is the in-order partition (kdtree.cpp:294-317) in its
+// rank-table form (part_* below); only the float mean (a sequential sum, kdtree.cpp:181-186) runs on one thread.
+// Everything works on a staged copy (`sv`, `si`).
 //
 // `C` (the cooperation policy) provides:
 //   int tid, nt;                      this thread, threads in the group
@@ -411,6 +414,8 @@ KD_FN int lazy_nearest(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n
 //   int* bcast;                       one int visible to the whole group
 //   void sync();                      group barrier (also orders memory)
 //   void minmax4(float* lo, float* hi) group-wide min of lo[0..3] / max of hi[0..3], result in every thread
+//   int exscan(int v, int* total)     group-wide exclusive prefix sum over tid, the total in every thread (has barriers)
+//   uint16_t* rank;                   `cap` entries for the partition's rank tables (NULL: sequential partition on thread 0)
 // With nt == 1 (host build, tests/host/kdreplay_host.cpp) this is a plain sequential program.
 template <class P, class I, class C>
 KD_FN void coop_boxes(const P& pts, const uint16_t* si, const float* sv, int c, int k0, int k1, C& co, float* tbox) {
@@ -479,6 +484,113 @@ KD_HD int partition_stream(float* v, uint16_t* ix, int n, float alpha) {
   return gl - 1;
 }
 
+// ---- data-parallel form of the same partition ---------------------------------------------------------------
+// The examination order above is an interleaving of two fixed streams -- the front stream a[0], a[1], ... and the
+// back stream a[n-1], a[n-2], ... -- so where every element ends up follows from prefix counts alone.  Call an
+// element "big" if !(v <= alpha) (it is moved away) and "kept" otherwise.  The front stream advances after every
+// kept element, so front element i is examined right after the i-th keep: a kept front element stays at slot i.
+// The k-th big front element (index P[k]) starts round k: it goes to the slot just left of the (k-1)-th kept
+// element from the right (index Q[k-1], Q[0] = n), then the back stream is consumed down to the k-th kept element
+// from the right (Q[k]); the big elements passed on the way each move one slot to the left and a[Q[k]] lands in
+// slot P[k].  Round k starts iff P[k] < Q[k-1] (monotone in k: K = number of rounds that start).  The last round
+// either completes (Q[K] > P[K]: the front stream then runs over kept elements up to F = Q[K]) or the back stream
+// meets the front inside it (F = P[K] + 1).  Elements below F belong to the front stream, the others to the back
+// stream.  T[0..NB) = P[1..NB], T[NB..n) = Q[1..NL] are the two rank tables (NB big, NL = n - NB kept elements).
+// Checked against partition_stream() element for element in tests/test_kdreplay_cpu.py.
+KD_HD bool part_big(float v, float alpha) { return !(v <= alpha); }
+
+KD_HD int part_count(const float* v, int k0, int k1, float alpha) {
+  int c = 0;
+  for (int k = k0; k < k1; k++) c += part_big(v[k], alpha) ? 1 : 0;
+  return c;
+}
+
+// bb0 = big elements in [0, k0)
+KD_HD void part_fill(const float* v, int k0, int k1, float alpha, int bb0, int NB, int n, uint16_t* T) {
+  const int NL = n - NB;
+  int bb = bb0;
+  for (int x = k0; x < k1; x++) {
+    if (part_big(v[x], alpha)) T[bb++] = (uint16_t)x;
+    else T[NB + (NL - (x - bb) - 1)] = (uint16_t)x;
+  }
+}
+
+KD_HD bool part_round_starts(const uint16_t* T, int NB, int n, int k) {      // 1 <= k <= NB
+  const int NL = n - NB;
+  const int Pk = (int)T[k - 1];
+  const int Qk1 = k == 1 ? n : (k - 1 <= NL ? (int)T[NB + k - 2] : -1);
+  return Pk < Qk1;
+}
+
+KD_HD int part_front(const uint16_t* T, int NB, int n, int K) {
+  if (K == 0) return n;
+  const int NL = n - NB;
+  const int PK = (int)T[K - 1];
+  if (K <= NL) { const int QK = (int)T[NB + K - 1]; if (QK > PK) return QK; }
+  return PK + 1;
+}
+
+// slot of element x after the partition; bb = big elements in [0, x)
+KD_HD int part_dest(const uint16_t* T, int NB, int n, int F, int x, bool big, int bb) {
+  if (x < F) {
+    if (!big) return x;
+    return (bb == 0 ? n : (int)T[NB + bb - 1]) - 1;          // Q[k-1] - 1 with k = bb + 1
+  }
+  if (big) return x - 1;
+  const int NL = n - NB;
+  return (int)T[NL - (x - bb) - 1];                           // P[k] with k = (kept elements right of x) + 1
+}
+
+KD_HD int kd_f2i(float f) { union { float f; int i; } u; u.f = f; return u.i; }
+KD_HD float kd_i2f(int i) { union { float f; int i; } u; u.i = i; return u.f; }
+
+// child boxes by membership (kept -> left child, big -> right child); the order inside a child does not matter
+template <class P, class I, class C>
+KD_FN void coop_boxes_split(const P& pts, const uint16_t* si, const float* sv, int c, int n, float alpha, C& co,
+                            float* lbox, float* rbox) {
+  float lo[4] = {3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f}, hi[4] = {-3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f};
+  for (int k = co.tid; k < n; k += co.nt) {
+    const float vc = sv[k];
+    const float vo = coord(pts, (int)si[k], 1 - c);
+    const float x = c == 0 ? vc : vo, y = c == 0 ? vo : vc;
+    const bool big = part_big(vc, alpha);                   // (no dynamic indexing: the arrays stay in registers)
+    const float xl = big ? 3.0e38f : x, yl = big ? 3.0e38f : y, xr = big ? x : 3.0e38f, yr = big ? y : 3.0e38f;
+    const float xL = big ? -3.0e38f : x, yL = big ? -3.0e38f : y, xR = big ? x : -3.0e38f, yR = big ? y : -3.0e38f;
+    lo[0] = xl < lo[0] ? xl : lo[0]; lo[1] = yl < lo[1] ? yl : lo[1]; lo[2] = xr < lo[2] ? xr : lo[2]; lo[3] = yr < lo[3] ? yr : lo[3];
+    hi[0] = xL > hi[0] ? xL : hi[0]; hi[1] = yL > hi[1] ? yL : hi[1]; hi[2] = xR > hi[2] ? xR : hi[2]; hi[3] = yR > hi[3] ? yR : hi[3];
+  }
+  co.minmax4(lo, hi);
+  lbox[0] = lo[0]; lbox[1] = hi[0]; lbox[2] = lo[1]; lbox[3] = hi[1];
+  rbox[0] = lo[2]; rbox[1] = hi[2]; rbox[2] = lo[3]; rbox[3] = hi[3];
+}
+
+// The group-wide partition of the staged range: writes the moved elements' indices to out[] (out[x] already holds
+// si[x]) and returns the split index.  Out of line: it is the rare path of a register-tight kernel.
+template <class I, class C>
+KD_COLD int partition_ranked(const float* sv, const uint16_t* si, int n, float alpha, I* out, C& co) {
+  // every thread owns a contiguous run of elements (odd length: conflict-free shared memory)
+  const int chunk = ((n + co.nt - 1) / co.nt) | 1;
+  const int k0 = co.tid * chunk < n ? co.tid * chunk : n, k1 = k0 + chunk < n ? k0 + chunk : n;
+  uint16_t* T = co.rank;
+  int NB = 0;
+  const int bb0 = co.exscan(part_count(sv, k0, k1, alpha), &NB);
+  part_fill(sv, k0, k1, alpha, bb0, NB, n, T);
+  co.sync();
+  int kc = 0;
+  for (int k = 1 + co.tid; k <= NB; k += co.nt) kc += part_round_starts(T, NB, n, k) ? 1 : 0;
+  int K = 0;
+  co.exscan(kc, &K);
+  const int F = part_front(T, NB, n, K);
+  int bb = bb0;
+  for (int x = k0; x < k1; x++) {
+    const bool big = part_big(sv[x], alpha);
+    const int d = part_dest(T, NB, n, F, x, big, bb);
+    if (d != x) out[d] = (I)si[x];
+    bb += big ? 1 : 0;
+  }
+  return n - NB - 1;
+}
+
 // Splits node `id` (uniform call).  Ranges larger than the staging capacity fall back to the sequential split
 // on thread 0.
 template <class P, class I, class C>
@@ -507,15 +619,30 @@ KD_FN int lazy_split_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int
     sv[k] = coord(pts, o, c);
   }
   co.sync();
-  if (co.tid == 0) {                                        // sequential by definition: float mean + partition
+  if (co.tid == 0) {                                        // the float mean is a sequential sum by definition (:181-186)
     float sum = 0.0f;
-    for (int k = 0; k < n; k++) sum += sv[k];
-    const float average = sum / (float)n;
-    *co.bcast = partition_stream(sv, si, n, average);
+    int k = 0;
+    for (; k + 8 <= n; k += 8) {                            // loads first, then the add chain in order
+      const float a0 = sv[k], a1 = sv[k + 1], a2 = sv[k + 2], a3 = sv[k + 3];
+      const float a4 = sv[k + 4], a5 = sv[k + 5], a6 = sv[k + 6], a7 = sv[k + 7];
+      sum += a0; sum += a1; sum += a2; sum += a3; sum += a4; sum += a5; sum += a6; sum += a7;
+    }
+    for (; k < n; k++) sum += sv[k];
+    *co.bcast = kd_f2i(sum / (float)n);
   }
   co.sync();
-  const int m = *co.bcast;                                  // last index (staged numbering) of the left child
-  for (int k = co.tid; k < n; k += co.nt) ind[l + k] = (I)si[k];
+  const float alpha = kd_i2f(*co.bcast);
+  int m;
+  bool by_flag = false;
+  if (co.rank != nullptr) {
+    m = partition_ranked<I, C>(sv, si, n, alpha, ind + l, co);
+    by_flag = true;
+  } else {
+    if (co.tid == 0) *co.bcast = partition_stream(sv, si, n, alpha);
+    co.sync();
+    m = *co.bcast;                                          // last index (staged numbering) of the left child
+    for (int k = co.tid; k < n; k += co.nt) ind[l + k] = (I)si[k];
+  }
   if (m >= n - 1 || m < 0) {
     // one side empty: the other child would be the node itself -> the reference recurses forever
     co.sync();
@@ -523,8 +650,12 @@ KD_FN int lazy_split_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int
   }
   if (*n_nodes + 2 > max_nodes) { co.sync(); return ERR_NODES; }
   float lbox[4], rbox[4];
-  coop_boxes<P, I, C>(pts, si, sv, c, 0, m, co, lbox);
-  coop_boxes<P, I, C>(pts, si, sv, c, m + 1, n - 1, co, rbox);
+  if (by_flag) {
+    coop_boxes_split<P, I, C>(pts, si, sv, c, n, alpha, co, lbox, rbox);
+  } else {
+    coop_boxes<P, I, C>(pts, si, sv, c, 0, m, co, lbox);
+    coop_boxes<P, I, C>(pts, si, sv, c, m + 1, n - 1, co, rbox);
+  }
   co.sync();                                                // everyone is done with the staging arrays and *n_nodes
   if (co.tid == 0) {
     LNode nd = nd0;

@@ -71,9 +71,45 @@ int kdr_nn_lazy(const double* pts, int n, const float* q, int nq, int32_t* idx, 
 struct HostCoop {
   int tid = 0, nt = 1;
   float* sv; uint16_t* si; int cap; int* bcast;
+  uint16_t* rank = nullptr;
   void sync() {}
   void minmax4(float*, float*) {}
+  int exscan(int v, int* total) { *total = v; return 0; }
 };
+
+// The rank-table partition run by `nt` emulated threads (phase by phase, like the barriers of the device code),
+// and the reference's sequential partition on the same input.  ix_* receive the permuted element indices; returns
+// the split index of the parallel form, *m_seq that of the sequential one.
+int kdr_partition_both(const float* v, int n, float alpha, int nt, uint16_t* ix_par, uint16_t* ix_seq, int* m_seq) {
+  std::vector<float> sv(v, v + n);
+  for (int k = 0; k < n; k++) ix_seq[k] = (uint16_t)k;
+  *m_seq = kdreplay::partition_stream(sv.data(), ix_seq, n, alpha);
+  std::vector<uint16_t> T(n > 0 ? n : 1);
+  const int chunk = ((n + nt - 1) / nt) | 1;
+  std::vector<int> cnt(nt), bb0(nt), k0(nt), k1(nt);
+  int NB = 0;
+  for (int t = 0; t < nt; t++) {
+    k0[t] = t * chunk < n ? t * chunk : n; k1[t] = k0[t] + chunk < n ? k0[t] + chunk : n;
+    cnt[t] = kdreplay::part_count(v, k0[t], k1[t], alpha);
+  }
+  for (int t = 0; t < nt; t++) { bb0[t] = NB; NB += cnt[t]; }
+  for (int t = 0; t < nt; t++) kdreplay::part_fill(v, k0[t], k1[t], alpha, bb0[t], NB, n, T.data());
+  int K = 0;
+  for (int t = 0; t < nt; t++)
+    for (int k = 1 + t; k <= NB; k += nt) K += kdreplay::part_round_starts(T.data(), NB, n, k) ? 1 : 0;
+  const int F = kdreplay::part_front(T.data(), NB, n, K);
+  for (int k = 0; k < n; k++) ix_par[k] = (uint16_t)k;          // like ind[l + x] == si[x] after the gather
+  for (int t = 0; t < nt; t++) {
+    int bb = bb0[t];
+    for (int x = k0[t]; x < k1[t]; x++) {
+      const bool big = kdreplay::part_big(v[x], alpha);
+      const int d = kdreplay::part_dest(T.data(), NB, n, F, x, big, bb);
+      if (d != x) ix_par[d] = (uint16_t)x;
+      bb += big ? 1 : 0;
+    }
+  }
+  return n - NB - 1;
+}
 
 int kdr_nn_lazy_coop(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis, int cap, int* nodes_built) {
   std::vector<kdreplay::Pt> p(n > 0 ? n : 1);
@@ -83,7 +119,9 @@ int kdr_nn_lazy_coop(const double* pts, int n, const float* q, int nq, int32_t* 
   std::vector<float> sv(cap > 0 ? cap : 1);
   std::vector<uint16_t> si(cap > 0 ? cap : 1);
   int nn = 0, bc = 0;
+  std::vector<uint16_t> rank(cap > 0 ? cap : 1);
   HostCoop co; co.sv = sv.data(); co.si = si.data(); co.cap = cap; co.bcast = &bc;
+  co.rank = cap & 1 ? nullptr : rank.data();             // an odd capacity selects the sequential partition
   kdreplay::PtrPts acc{p.data()};
   int rc = kdreplay::lazy_init_coop(acc, n, ind.data(), nodes.data(), &nn, co);
   if (rc != kdreplay::OK) return -1000 - rc;

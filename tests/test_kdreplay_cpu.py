@@ -63,7 +63,7 @@ def test_eager_and_lazy_search_match_reference(kd, oracle):
         assert built.value <= oracle.tree(pts)[0]        # the lazy tree never holds more nodes than the full one
 
 
-@pytest.mark.parametrize("cap", [1 << 16, 300])
+@pytest.mark.parametrize("cap", [1 << 16, 300, (1 << 16) + 1, 301])   # odd: sequential partition
 def test_cooperative_lazy_search_matches_reference(kd, oracle, cap):
     """The L2 kernel's cooperative split (staged gather, sequential mean + partition, parallel child boxes)."""
     for pts, q in clouds():
@@ -74,3 +74,37 @@ def test_cooperative_lazy_search_matches_reference(kd, oracle, cap):
         assert kd.kdr_nn_lazy_coop(pts.ctypes.data_as(P), n, q.ctypes.data_as(P), nq, idx.ctypes.data_as(P),
                                    dis.ctypes.data_as(P), cap, C.byref(built)) == 0
         assert (idx == ridx).all() and (dis == rdis).all()
+
+
+def test_rank_table_partition_equals_the_sequential_partition(kd):
+    """part_* (kdreplay.h): the data-parallel form of select_on_coordinate_value writes the very permutation the
+    reference's swap loop (kdtree.cpp:294-317) produces -- every n up to 40 with random patterns, all 2^n patterns up
+    to n = 10, long arrays, all-kept / all-moved / single-element edge cases, NaN, 1..1024 emulated threads."""
+    rng = np.random.default_rng(5)
+    U16 = C.POINTER(C.c_uint16)
+    def check(v, alpha, nt):
+        v = np.ascontiguousarray(v, np.float32)
+        n = len(v)
+        a = np.zeros(max(n, 1), np.uint16); b = np.zeros(max(n, 1), np.uint16)
+        ms = C.c_int(-9)
+        mp = kd.kdr_partition_both(v.ctypes.data_as(C.POINTER(C.c_float)), n, C.c_float(alpha), nt,
+                                   a.ctypes.data_as(U16), b.ctypes.data_as(U16), C.byref(ms))
+        assert mp == ms.value, (n, nt, v.tolist())
+        assert np.array_equal(a[:n], b[:n]), (n, nt, v.tolist(), a[:n].tolist(), b[:n].tolist())
+    for n in range(1, 11):
+        for bits in range(1 << n):
+            v = np.array([(bits >> i) & 1 for i in range(n)], np.float32)
+            check(v, 0.5, 1); check(v, 0.5, 3)
+    for n in range(1, 41):
+        for _ in range(30):
+            check(rng.integers(0, 2, n), 0.5, int(rng.integers(1, 9)))
+    for n in (1000, 4097, 32768, 65535):
+        for frac in (0.5, 0.02, 0.98):
+            v = (rng.random(n) < frac).astype(np.float32)
+            for nt in (1, 32, 1024):
+                check(v, 0.5, nt)
+        check(np.zeros(n), 0.5, 1024); check(np.ones(n), 0.5, 1024)
+        w = rng.normal(size=n).astype(np.float32)
+        check(w, float(w.mean()), 1024)
+    w = rng.normal(size=500).astype(np.float32); w[::7] = np.nan
+    check(w, 0.0, 64)
