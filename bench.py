@@ -160,6 +160,31 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------- GPU arm -------
+def bind_near_gpu(local_rank):
+    """Pins this rank to the CPUs that are local to its GPU (sysfs local_cpulist of the PCI device) BEFORE the pinned
+    host buffers are allocated and filled, so that their pages land on the GPU's NUMA node (first touch).  With 8 ranks
+    copying at once the host side is the bottleneck of the end-to-end leg.  Returns what it did, for the JSON line."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local_rank)
+        bus = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = open("/sys/bus/pci/devices/%s/numa_node" % bus).read().strip()
+        txt = open("/sys/bus/pci/devices/%s/local_cpulist" % bus).read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if "-" in part:
+                a, b = part.split("-"); cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        want = cpus & os.sched_getaffinity(0)
+        if not want:
+            return {"numa_node": node, "bound": False, "why": "no local CPU in this process's affinity mask"}
+        os.sched_setaffinity(0, want)
+        return {"numa_node": node, "bound": True, "cpus": len(want)}
+    except Exception as e:       # no sysfs entry (VM), old torch: run unbound
+        return {"bound": False, "why": str(e)[:80]}
+
+
 def load_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -201,6 +226,7 @@ def gpu_arm(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
+    numa = bind_near_gpu(local_rank) if args.numa_bind else {"bound": False, "why": "--no-numa-bind"}
     c3 = args.workload == "c3"
     if c3:       # the whole loop-closure batch is split over the ranks (strong scaling)
         seed_lo, n_pairs = sharding.shard_seeds(C3_SEED0, args.total_pairs, rank, world)
@@ -312,7 +338,7 @@ def gpu_arm(args, rank, world, local_rank):
                    "collective": "nccl all_gather of 160 B records" if world > 1 else "none"},
         "e2e": {"value": world * n_pairs / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                 "d2h_bytes_per_step": d2h * world, "ms_per_step": e2e_ms,
-                "api": "ccicp_register_batch (C ABI, pinned host buffers)"},
+                "api": "ccicp_register_batch (C ABI, pinned host buffers)", "host_numa": numa},
         # kernels of this library launched inside the two timed regions (device leg + host-buffer leg), all ranks
         "gpu_launches": (int(li.n_launches) + e2e_launches) * args.steps * world,
         "gpu_launches_detail": {"device_leg_per_step": int(li.n_launches), "e2e_leg_per_step": e2e_launches},
@@ -344,6 +370,8 @@ def main():
                          "c3: --total-pairs loop-closure candidates split over the GPUs, records gathered over NCCL")
     ap.add_argument("--total-pairs", type=int, default=C3_TOTAL, help="c3 only: pairs of the whole job")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", dest="numa_bind", action="store_false",
+                    help="do not pin the rank to its GPU's local CPUs before allocating the pinned host buffers")
     ap.add_argument("--cpu-pairs-per-core", type=int, default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

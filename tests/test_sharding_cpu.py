@@ -60,3 +60,27 @@ def test_gather_records_gloo(world, n_total):
         p.join(timeout=60)
     assert sorted(r[0] for r in res) == list(range(world))
     assert all(r[1] for r in res) and all(r[2] == float(world) for r in res)
+
+
+def test_bench_c3_shards_and_chunked_generation():
+    """bench.py --workload c3: the ranks' shards of the loop-closure batch are exactly the batch (same seeds, same
+    scans, same noisy initial poses), and the chunked generator packs the same CSR arrays as one call."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from slam_b200 import scangen
+    plain = lambda shape, dt: np.zeros(shape, dt)
+    total, world = 24, 3
+    whole = scangen.generate(bench.C3_SEED0, total, config=3)
+    parts = []
+    for r in range(world):
+        lo, n = sharding.shard_seeds(bench.C3_SEED0, total, r, world)
+        parts.append(bench.generate_chunked(lo, n, 3, plain, chunk=3))       # 8 pairs per rank in chunks of 3, 3, 2
+    assert np.array_equal(np.concatenate([p.seeds for p in parts]), whole.seeds)
+    assert np.array_equal(np.concatenate([p.model_xy for p in parts]), whole.model_xy)
+    assert np.array_equal(np.concatenate([p.scene_xy for p in parts]), whole.scene_xy)
+    assert np.array_equal(np.concatenate([p.init for p in parts]), whole.init)
+    off = np.concatenate([[0]] + [p.model_off[1:] + sum(len(q.model_xy) for q in parts[:i]) for i, p in enumerate(parts)])
+    assert np.array_equal(off, whole.model_off)
+    # C3's initial poses are the truth plus noise, not the identity of C2
+    assert np.abs(whole.init - whole.truth).max() > 0 and np.abs(whole.init).max() > 0
