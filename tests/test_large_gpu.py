@@ -51,6 +51,27 @@ def test_forced_l2_lockstep_with_ties(l2ctx, oracle):
     assert (res["status"] & capi.ST_TIE_REPLAY).any()
 
 
+def test_l2_tie_replay_on_large_lattice(ctx, oracle):
+    """16384-point lattice (L2 variant by size): every query is equidistant from four model points, so each one is
+    answered by the cooperative kd-tree replay (first iteration) -- the data-parallel partition (kdreplay.h: partition_ranked) splits
+    nodes from 14384 points down to the leaves, the 2000-point class exercises ranges shorter than the CTA.  The
+    correspondences of two lock-step iterations must be the reference's, index for index."""
+    g = np.arange(128, dtype=np.float64) * 0.1
+    model = np.stack(np.meshgrid(g, g), -1).reshape(-1, 2)
+    rng = np.random.default_rng(11)
+    pick = np.sort(rng.choice(len(model), 1500, replace=False))
+    scene = model[pick] + 0.05
+    nGA = 2000
+    pair = (model[:nGA], model[nGA:], scene[pick < nGA], scene[pick >= nGA])
+    Rt0 = np.array([1.0, 0, 0, 1, 0, 0])
+    tr = oracle.trace(*pair, Rt0, max_iter=2, min_delta=-2.0)
+    corr, res = gpu_lockstep_corr(ctx, pair, tr["Rt_trace"][:-1])
+    assert ctx.launch_info().kernel_variant == 1
+    assert (corr == tr["corr"]).all()
+    assert (res["status"][0] & capi.ST_TIE_REPLAY) and not (res["status"] & capi.ST_TREE_OVERFLOW).any()
+    assert int(res["n_tie_replays"][0]) == int(tr["tie"][0].sum()) >= 900      # (float rounding breaks a third of the ties)
+
+
 def test_c4_dense_pair(ctx, oracle):
     """Config C4: one 32768-beam pair (does not fit shared memory -> L2 variant), 30 fixed iterations."""
     b = scangen.generate(5000, 2, config=4)
