@@ -179,10 +179,10 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
   __syncthreads();
 }
 
-// ---- tie replay (rare): rebuild the reference kd-tree, re-answer tied queries
-// The build is the reference's sequential algorithm (float mean split, in-order partition), so it runs on
-// one thread per class; its working set (points via kinv -> mpts, permutation kind) lives in shared memory
-// and only the node records go to a per-CTA global scratch.
+// ---- tie replay (rare): rebuild the reference kd-tree along the visited paths, re-answer tied queries
+// The build reproduces the reference's algorithm (sequential float mean, in-order partition in its data-parallel
+// form); the points are reached via kinv -> mpts, the permutation is kind, the node records go to a per-CTA global
+// scratch.
 struct SmemPts {
   const float2* mpts; const uint16_t* inv;
   __device__ __forceinline__ kdreplay::Pt operator()(int i) const {
@@ -200,51 +200,9 @@ __host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
   return replay_nodes_bytes(max_model) + align_up((size_t)(max_model + 16) * sizeof(uint16_t), 16);
 }
 
-// Tied queries are listed in s.tiebits.  Thread c (c = 0 GA, 1 NGA) replays the tied queries of its class one
-// after the other on the class's lazily materialised reference kd-tree (kdreplay.h): the partition work is
-// sequential by definition, and ties are rare (about 1e-7 per query on scan data), so latency is what counts.
-// Inlined (like replay_ties_coop below): +3 % on C2 over the out-of-line call (1.02 -> 1.05 M reg/s).
-template <int kThreads>
-__device__ __forceinline__ void replay_ties(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid) {
-  __syncthreads();
-  if (tid < 2 && s.grid[tid].G > 0) {
-    const GridP g = s.grid[tid];
-    kdreplay::LNode* nodes = (kdreplay::LNode*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta) + 2 * g.first + 8 * tid;
-    const int max_nodes = 2 * g.n + 8;
-    const SmemPts pts{s.mpts, s.kinv + g.first};
-    uint16_t* ind = s.kind + g.first;
-    int nn = s.misc[M_NNODE + tid];
-    int state = s.misc[M_TREE + tid];
-    const int i0 = tid ? nsGA : 0, i1 = tid ? ns : nsGA;
-    for (int w = i0 >> 5; w <= (i1 - 1) >> 5 && i1 > i0; w++) {
-      uint32_t bits = s.tiebits[w];
-      while (bits) {
-        const int b = __ffs(bits) - 1;
-        bits &= bits - 1;
-        const int i = (w << 5) + b;
-        if (i < i0 || i >= i1) continue;
-        if (state == 0) state = (kdreplay::lazy_init(pts, g.n, ind, nodes, &nn) == kdreplay::OK) ? 1 : 2;
-        if (state != 1) continue;                  // tree unavailable: keep the grid's answer
-        const double2 sp = s.scene[i];
-        float qx, qy;
-        transform(Rt, sp.x, sp.y, qx, qy);
-        int32_t o = -1; float d = 0.0f;
-        const int rc = kdreplay::lazy_nearest(pts, ind, nodes, max_nodes, &nn, qx, qy, &o, &d);
-        if (rc != kdreplay::OK || o < 0) { state = 2; continue; }
-        s.slots[i] = s.kinv[g.first + o];
-        atomicAdd(&s.misc[M_REPLAYS], 1);
-      }
-    }
-    s.misc[M_NNODE + tid] = nn;
-    s.misc[M_TREE + tid] = state;
-    if (state == 2) atomicOr(&s.misc[M_TREEFAIL], 1);
-  }
-  __syncthreads();
-  for (int w = tid; w <= (ns - 1) >> 5; w += kThreads) s.tiebits[w] = 0u;
-  __syncthreads();
-}
-
-// ---- cooperative tie replay (L2 variant): the whole CTA walks the tied queries one at a time --------------
+// ---- cooperative tie replay: the whole CTA walks the tied queries (listed in s.tiebits) one at a time ----------
+// Both kernel variants use it.  (A one-thread-per-class replay used to serve the on-chip variant: 0.1-0.3 ms for the
+// first tie of a pair, which made a tie in one of the last pairs of a launch the kernel's tail.)
 template <int kThreads>
 struct CtaCoop {
   int tid, nt;
@@ -295,7 +253,8 @@ struct CtaCoop {
 // the C4 wave went from 17.7 to 22.4 ms; inlined it is 17.4 ms (the cold block is spilled around, not through).
 template <int kThreads>
 __device__ __forceinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s, const double* Rt, int ns, int nsGA, int tid,
-                                              char* stage, int stage_cap, float* fred) {
+                                              char* stage, int stage_cap, float* fred, const double2* scene,
+                                              uint16_t* rank_base) {
   __syncthreads();
   for (int cls = 0; cls < 2; cls++) {
     if (s.grid[cls].G == 0) continue;
@@ -308,7 +267,8 @@ __device__ __forceinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s
     co.tid = tid; co.nt = kThreads; co.cap = stage_cap;
     co.sv = (float*)stage; co.si = (uint16_t*)(stage + (size_t)stage_cap * 4);
     co.bcast = &s.misc[15]; co.fred = fred;
-    co.rank = (uint16_t*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta + replay_nodes_bytes(a.max_model)) + g.first;
+    co.rank = (rank_base ? rank_base
+                         : (uint16_t*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta + replay_nodes_bytes(a.max_model))) + g.first;
     int* nn = &s.misc[M_NNODE + cls];
     int state = s.misc[M_TREE + cls];
     const int i0 = cls ? nsGA : 0, i1 = cls ? ns : nsGA;
@@ -321,7 +281,7 @@ __device__ __forceinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s
         if (i < i0 || i >= i1) continue;
         if (state == 0) state = (kdreplay::lazy_init_coop(pts, g.n, ind, nodes, nn, co) == kdreplay::OK) ? 1 : 2;
         if (state != 1) continue;                  // tree unavailable: keep the grid's answer
-        const double2 sp = s.scene[i];
+        const double2 sp = scene[i];
         float qx, qy;
         transform(Rt, sp.x, sp.y, qx, qy);
         int32_t o = -1; float d = 0.0f;

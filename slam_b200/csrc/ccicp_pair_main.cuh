@@ -220,7 +220,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
   __shared__ double red_s[2 * kWarps * kRedStride];
-  __shared__ double rtprev_s[8 + (kGlobal ? kWarps * 4 : 0)];     // + float[kWarps][8] min/max scratch of the tie replay
+  __shared__ double rtprev_s[8 + kWarps * 4];     // + float[kWarps][8] min/max / scan scratch of the tie replay
   __shared__ double exact_s[kExact ? 16 : 1];
   __shared__ GridP grid_s[2];
   __shared__ int misc_s[16];
@@ -317,8 +317,20 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
 #pragma unroll
           for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&red[w * 10 + 8]; n += ip[0]; any_tie |= ip[1]; }
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
-            if (kGlobal) replay_ties_coop<kThreads>(a, s, Rt, ns, nsGA, tid, smem_raw, a.stage_cap, (float*)rtprev_s + 16);
-            else replay_ties<kThreads>(a, s, Rt, ns, nsGA, tid);
+            if (kGlobal) {
+              replay_ties_coop<kThreads>(a, s, Rt, ns, nsGA, tid, smem_raw, a.stage_cap, (float*)rtprev_s + 16, s.scene, nullptr);
+            } else {
+              // On chip the whole CTA replays too (one thread per class used to: 0.1-0.3 ms for the first tie of a pair,
+              // and a tie in one of the last pairs of a launch is the kernel's tail -- the 14 replays of the C2 batch
+              // cost 0.17 ms of 3.85).  The staging arrays and the rank table take the place of the scene copy, which is
+              // read from the input for the tied queries and reloaded afterwards (same thread -> same points).
+              const double2* src = (const double2*)a.scene_xy + s0;
+              __syncthreads();
+              replay_ties_coop<kThreads>(a, s, Rt, ns, nsGA, tid, s.region0, a.mcap, (float*)rtprev_s + 16, src,
+                                         (uint16_t*)(s.region0 + (size_t)a.mcap * 6));
+              double2* dst = (double2*)s.region0;
+              for (int i = tid; i < ns; i += kThreads) dst[i] = __ldg(src + i);
+            }
             status |= CCICP_ST_TIE_REPLAY;
             sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);
             const int wc = __reduce_add_sync(0xffffffffu, cnt);
