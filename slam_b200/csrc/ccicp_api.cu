@@ -45,6 +45,9 @@ struct ccicp_ctx {
   std::string last_err;
 };
 
+#ifndef CCICP_ITEMS_PER_CTA
+#define CCICP_ITEMS_PER_CTA 32
+#endif
 namespace {
 
 int fail_cuda(ccicp_ctx* ctx, cudaError_t e, const char* what) {
@@ -142,7 +145,10 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   const bool best_of = (prm->flags & CCICP_F_BEST_OF_SEEDS) && n_seeds > 1;
   int items_per_pair = 1, seeds_per_item = n_seeds;
   if (n_seeds > 1) {
-    long long want = (4LL * resident + n_pairs - 1) / n_pairs;
+    // >= CCICP_ITEMS_PER_CTA items per resident CTA: a CTA runs a whole number of items, so with 4 per CTA (65536 problems of config C5 =
+    // 2560 items of 26 seeds on 592 CTAs) the launch lasted 5 item times where 4.3 were needed; the grid build an item
+    // repeats is ~4 % of ONE seed's work
+    long long want = ((long long)CCICP_ITEMS_PER_CTA * resident + n_pairs - 1) / n_pairs;
     if (want < 1) want = 1;
     if (want > n_seeds) want = n_seeds;
     seeds_per_item = (int)((n_seeds + want - 1) / want);
