@@ -124,7 +124,10 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : icp_pair_l2_kernel;
   cudaFuncAttributes fa_on;
   CK(cudaFuncGetAttributes(&fa_on, k_on));
-  size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false);
+  // CCICP_F_TRIM: one u32 per scene point behind the carved working set (this iteration's squared distances, the keys
+  // of the radix select)
+  const size_t warm_bytes = trim ? align_up((size_t)a.scap * 4, 128) : 0;
+  size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false) + warm_bytes;
   const bool use_l2 = smem + fa_on.sharedSizeBytes > (size_t)ctx->max_smem_optin || ctx->force_l2;
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
   int occ = 0;
@@ -175,7 +178,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   }
 
   if (use_l2) {
-    a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true);
+    a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true) + warm_bytes;
     const size_t ws_slot = a.workspace_per_cta * (size_t)resident;
     if (ctx->workspace.cap < ws_slot * 4) {
       if (slot != 0) return CCICP_E_INVALID;

@@ -153,27 +153,34 @@ __device__ __noinline__ void exact_step(const Smem& s, const double* Rt, int ns,
 // k = ceil(trim_frac * n_gated), found by a 4 x 8-bit radix select over the (non-negative, hence order-preserving) float
 // bit patterns in shared memory; correspondences at the threshold distance are all kept.  A trimmed scene point is
 // treated like an ungated one from here on (slot = none: no part in the sums, the indices, the score, the information
-// matrix, and no warm start next iteration).  The distance is recomputed with the search's own float expression.
+// matrix); its match only serves as the starting bound of the next iteration's search.  The distances are computed once
+// per call with the search's own float expression and kept as the select's keys.
 template <int kThreads>
-__device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double* Rt, int ns, int tid, uint32_t* th) {
-  auto key_of = [&](int i, unsigned slot) -> uint32_t {
-    const double2 sp = s.scene[i];
-    float qx, qy;
-    transform(Rt, sp.x, sp.y, qx, qy);
-    const float2 p = s.mpts[slot];
-    const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
-    return __float_as_uint(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-  };
+__device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double* Rt, int ns, int tid, uint32_t* th,
+                                         uint32_t* keys) {
+  // keys[i] = bit pattern of the gated squared distance of scene point i, computed once (0xFFFFFFFF = not gated: never
+  // matches a prefix because a finite float's top byte is < 0xFF); every thread reads back only what it wrote
+  for (int i = tid; i < ns; i += kThreads) {
+    const unsigned slot = s.slots[i];
+    uint32_t key = 0xFFFFFFFFu;
+    if (slot != kNoSlot) {
+      const double2 sp = s.scene[i];
+      float qx, qy;
+      transform(Rt, sp.x, sp.y, qx, qy);
+      const float2 p = s.mpts[slot];
+      const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
+      key = __float_as_uint(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+    }
+    keys[i] = key;
+  }
   uint32_t prefix = 0, mask = 0;
   for (int pass = 3; pass >= 0; pass--) {
     __syncthreads();
     if (tid < 256) th[tid] = 0;
     __syncthreads();
     for (int i = tid; i < ns; i += kThreads) {
-      const unsigned slot = s.slots[i];
-      if (slot == kNoSlot) continue;
-      const uint32_t key = key_of(i, slot);
-      if ((key & mask) == prefix) atomicAdd(&th[(key >> (8 * pass)) & 255u], 1u);
+      const uint32_t key = keys[i];
+      if (key != 0xFFFFFFFFu && (key & mask) == prefix) atomicAdd(&th[(key >> (8 * pass)) & 255u], 1u);
     }
     __syncthreads();
     if (tid < 32) {
@@ -201,17 +208,22 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double
       if (tid == 0) th[258] = total;
     }
     __syncthreads();
-    if (th[258] == 0) return;                              // nothing gated: nothing to trim (uniform)
+    if (th[258] == 0) return;                              // nothing gated: nothing to trim (uniform; all keys are 'none')
     prefix |= th[256] << (8 * pass);
     mask |= 0xFFu << (8 * pass);
   }
+  // From here on keys[i] is the search's starting slot for the next iteration: the match of a trimmed point (still
+  // the best guess; the search is exact whatever the start), none otherwise.  Without it the trimmed points paid for a
+  // cold search every iteration (C2, trim_frac 0.7: 9.6 ms against 6.3 ms with nothing trimmed).
   for (int i = tid; i < ns; i += kThreads) {
-    const unsigned slot = s.slots[i];
-    if (slot == kNoSlot) continue;
-    if (key_of(i, slot) > prefix) {
+    const uint32_t key = keys[i];
+    uint32_t start = kNoSlot;
+    if (key != 0xFFFFFFFFu && key > prefix) {
+      start = s.slots[i];
       s.slots[i] = (uint16_t)kNoSlot;
       atomicAnd(&s.tiebits[i >> 5], ~(1u << (i & 31)));
     }
+    keys[i] = start;
   }
 }
 
@@ -227,6 +239,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   __shared__ uint32_t trim_s[kTrim ? 260 : 1];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
   Smem s = carve<kGlobal>(base, a.mcap, a.scap, a.ccap, red_s, rtprev_s, grid_s, misc_s);
+  uint32_t* trim_keys = nullptr;       // kTrim: [scap] behind the carved working set
+  if constexpr (kTrim) {
+    trim_keys = (uint32_t*)(base + workset_bytes(a.mcap, a.scap, a.ccap, kGlobal));
+    if (!kGlobal) __builtin_assume(__isShared(trim_keys));
+  }
   const int tid = threadIdx.x;
   const float gate_f = __double2float_ru(a.indist);
   const bool replay_on = !(a.flags & CCICP_F_NO_TIE_REPLAY);
@@ -274,6 +291,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
       __syncthreads();
       if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; }
       for (int i = tid; i < ns; i += kThreads) s.slots[i] = (uint16_t)kNoSlot;   // no warm start for a new seed
+      if constexpr (kTrim) { for (int i = tid; i < ns; i += kThreads) trim_keys[i] = kNoSlot; }
       for (int w = tid; w <= (ns - 1) >> 5 && ns > 0; w += kThreads) s.tiebits[w] = 0u;
       __syncthreads();
 
@@ -295,7 +313,9 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search<kGlobal>(s.mpts, s.cstart, g, qx, qy, gate_f, s.slots[i], best, bslot, tie);
+              unsigned start = s.slots[i];
+              if constexpr (kTrim) { if (start == kNoSlot) start = trim_keys[i] & 0xFFFFu; }
+              nn_search<kGlobal>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie);
               if (bslot >= 0 && (double)best < a.indist) {
                 slot = (unsigned)bslot;
                 if (tie && replay_on) { pend = 1; atomicOr(&s.tiebits[i >> 5], 1u << (i & 31)); }
@@ -303,7 +323,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             }
             s.slots[i] = (uint16_t)slot;
           }
-          if constexpr (kTrim) trim_select<kThreads>(a, s, Rt, ns, tid, trim_s);
+          if constexpr (kTrim) trim_select<kThreads>(a, s, Rt, ns, tid, trim_s, trim_keys);
           double v[8];
           int cnt;
           sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);        // loop B: converged accumulation
@@ -411,7 +431,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             }
             s.slots[i] = (uint16_t)slot;
           }
-          if constexpr (kTrim) trim_select<kThreads>(a, s, P, ns, tid, trim_s);
+          if constexpr (kTrim) trim_select<kThreads>(a, s, P, ns, tid, trim_s, trim_keys);
         }
         const bool want_info = (a.flags & CCICP_F_INFO) != 0;
         const bool fixed_dy = (a.flags & CCICP_F_INFO_FIXED_DY) != 0;
