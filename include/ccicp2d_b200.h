@@ -159,7 +159,12 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
  * work is enqueued on `stream` (a cudaStream_t cast to void*; NULL = the
  * ctx's own stream) without synchronising.  max_model / max_scene are the
  * largest per-pair point counts (GA+NGA) in the batch, max_cells_hint may be
- * 0.  Use ccicp_stream_sync (or your own event) before reading results.      */
+ * 0.  Use ccicp_stream_sync (or your own event) before reading results.
+ * A ctx serves ONE in-flight call at a time: its work counter, tie-replay scratch, L2 workspace and best-of-seeds
+ * staging are per-ctx (and may be re-allocated by the next call), so a second call on the same ctx -- from
+ * another thread or on another stream -- must wait until the first has completed.  Use one ctx per host thread /
+ * stream (ctxs are cheap; several may share a device).  A pair whose real size exceeds max_model / max_scene (or
+ * the cell hint) is not registered: status CCICP_ST_HINT_TOO_SMALL, R,t unchanged, corr_idx -1.               */
 int ccicp_register_batch_device(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
                                 const double* d_model_xy, const int32_t* d_model_off,
                                 const double* d_scene_xy, const int32_t* d_scene_off,

@@ -71,8 +71,9 @@ def fit(mGA, mNGA, sGA, sNGA, Rt0, max_iter=30, min_delta=-2.0, indist=5.0, want
     return dict(Rt=Rt, num_corr=nc.value, status=st, info=eW if want_info else None)
 
 
-def trace(mGA, mNGA, sGA, sNGA, Rt0, max_iter=30, min_delta=-2.0, indist=5.0, want_info=False, kind=None):
-    """Lock-step trace.  Returns dict with Rt_trace[iters+1,6], corr[iters,ns], dis, tie, ncorr, delta, iters."""
+def trace(mGA, mNGA, sGA, sNGA, Rt0, max_iter=30, min_delta=-2.0, indist=5.0, want_info=False, kind=None, want_tie=True):
+    """Lock-step trace.  Returns dict with Rt_trace[iters+1,6], corr[iters,ns], dis, tie, ncorr, delta, iters.
+    want_tie=False skips the brute-force tie count (O(n_model) per query: minutes on 32768-point pairs)."""
     f = load(kind)["trace"]
     mGA, mNGA, sGA, sNGA = _c(mGA), _c(mNGA), _c(sGA), _c(sNGA)
     ns = len(sGA) + len(sNGA)
@@ -86,7 +87,7 @@ def trace(mGA, mNGA, sGA, sNGA, Rt0, max_iter=30, min_delta=-2.0, indist=5.0, wa
     iters = C.c_int(0)
     eW = np.zeros(9, np.float64)
     st = f(_p(mGA), len(mGA), _p(mNGA), len(mNGA), _p(sGA), len(sGA), _p(sNGA), len(sNGA), max_iter, min_delta,
-           indist, _p(Rt0), _p(Rt_trace), _p(corr), _p(dis), _p(tie), _p(ncorr), _p(delta), C.addressof(iters),
+           indist, _p(Rt0), _p(Rt_trace), _p(corr), _p(dis), _p(tie) if want_tie else None, _p(ncorr), _p(delta), C.addressof(iters),
            _p(eW) if want_info else None)
     k = iters.value
     return dict(status=st, iters=k, Rt_trace=Rt_trace[:k + 1], corr=corr[:k, :ns], dis=dis[:k, :ns],

@@ -120,8 +120,18 @@ def build_oracle(force=False, verbose=False):
         _run(["make", "-C", od, "ref"] + (["-B"] if force else []), verbose)
 
 
+def build_tools(force=False, verbose=False):
+    """profiles/fp32_peak: micro-benchmark of the un-fused FP32 issue peak (denominator of bench.py's roofline_useful)."""
+    src = os.path.join(ROOT, "profiles", "fp32_peak.cu")
+    out = os.path.join(ROOT, "profiles", "fp32_peak")
+    if os.path.exists(src) and (force or _newer(out, [src])):
+        _run([nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-o", out, src], verbose)
+    return out
+
+
 def build_all(force=False, verbose=False):
     build_cuda(force, verbose)
+    build_tools(force, verbose)
     build_scangen(force, verbose)
     build_facade(force, verbose)
     build_host_tests(force, verbose)

@@ -1,8 +1,9 @@
 """ctypes binding of include/ccicp2d_b200.h (libccicp2d_b200.so).
 
 The product path has no CPU fallback: if the library is missing, or there is no
-sm_100 device, these calls raise.  Host mirror of the reference's interface for
-the path lives in slam_b200/registration.py.
+sm_100 device, these calls raise.  The host mirror of the reference's C++ interface for the
+path is the facade library (include/ccicp2d/*.h, slam_b200/csrc/facade/icp_facade.cpp); this
+module is test / bench orchestration only.
 """
 import ctypes as C
 import os

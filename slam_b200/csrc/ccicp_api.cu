@@ -92,7 +92,8 @@ int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
 // worst-case number of grid cells for a pair with at most max_model model points
 int max_cells_for(int max_model) {
-  static const int lows[] = {0, 4, 33, 129, 513};
+  // one candidate per step of grid_side(): the smaller class just above each threshold, the rest in the other class
+  static const int lows[] = {0, 4, 33, 129, 513, 2049, 8193};
   int best = 0;
   for (int a : lows) {
     if (a > max_model) break;
@@ -107,7 +108,9 @@ int max_cells_for(int max_model) {
 int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy, const int32_t* d_model_off,
                const double* d_scene_xy, const int32_t* d_scene_off, const double* d_init_Rt,
                const ccicp_params* prm, ccicp_result* d_out, int32_t* d_corr, int32_t max_model, int32_t max_scene,
-               int32_t max_cells, int64_t total_scene, cudaStream_t st) {
+               int32_t max_cells, int64_t total_scene, cudaStream_t st, int n_slots = 1) {
+  // n_slots = launches of this call that may be in flight together (chunked host path: up to 4); each gets its own
+  // tie-replay scratch and L2 workspace, sized by the first launch of the call
   if (slot == 0) ctx->info.n_launches = 0;
   if (n_pairs == 0) return CCICP_OK;
   if (max_model > CCICP_MAX_POINTS - 1 || max_scene > CCICP_MAX_POINTS) return CCICP_E_TOO_LARGE;
@@ -171,26 +174,26 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   if (rc) return rc;
   const size_t per_cta = replay_scratch_bytes(max_model);
   const size_t per_slot = per_cta * (size_t)resident;
-  if (ctx->scratch.cap < per_slot * 4) {
+  if (ctx->scratch.cap < per_slot * n_slots) {
     if (slot != 0) return CCICP_E_INVALID;      // sized by the first launch of a call
-    rc = reserve(ctx, ctx->scratch, per_slot * 4);
+    rc = reserve(ctx, ctx->scratch, per_slot * n_slots);
     if (rc) return rc;
   }
 
   if (use_l2) {
     a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true) + warm_bytes;
     const size_t ws_slot = a.workspace_per_cta * (size_t)resident;
-    if (ctx->workspace.cap < ws_slot * 4) {
+    if (ctx->workspace.cap < ws_slot * n_slots) {
       if (slot != 0) return CCICP_E_INVALID;
-      rc = reserve(ctx, ctx->workspace, ws_slot * 4);
+      rc = reserve(ctx, ctx->workspace, ws_slot * n_slots);
       if (rc) return rc;
     }
-    a.workspace = (char*)ctx->workspace.p + (size_t)(slot & 3) * ws_slot;
+    a.workspace = (char*)ctx->workspace.p + (size_t)(slot % n_slots) * ws_slot;
   }
   a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
   a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
   a.work_counter = (int32_t*)ctx->counter.p + (slot & 15);
-  a.scratch = (char*)ctx->scratch.p + (size_t)(slot & 3) * per_slot; a.scratch_per_cta = per_cta;
+  a.scratch = (char*)ctx->scratch.p + (size_t)(slot % n_slots) * per_slot; a.scratch_per_cta = per_cta;
   a.pair_base = pair_base;
   a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
   a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
@@ -446,7 +449,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
     rc = launch_icp(ctx, p0, c, p1 - p0, n_seeds, (const double*)ctx->d_model.p, (const int32_t*)ctx->d_moff.p,
                     (const double*)ctx->d_scene.p, (const int32_t*)ctx->d_soff.p, (const double*)ctx->d_init.p, params,
                     (ccicp_result*)ctx->d_out.p, corr_idx ? (int32_t*)ctx->d_corr.p : nullptr, max_model, max_scene,
-                    max_cells, n_scene, ks);
+                    max_cells, n_scene, ks, n_chunks < 4 ? n_chunks : 4);
     if (rc) { cudaDeviceSynchronize(); return rc; }
     if (c == n_chunks - 1) CK(cudaEventRecord(ctx->ev[4], ks));
     const size_t o0 = best_of ? (size_t)p0 : (size_t)p0 * n_seeds, o1 = best_of ? (size_t)p1 : (size_t)p1 * n_seeds;

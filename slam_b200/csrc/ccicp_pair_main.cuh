@@ -192,6 +192,7 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double
       for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += t; }
       const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
       uint32_t k = th[257];
+      __syncwarp();                                        // every lane has read the carried rank before one lane replaces it
       if (pass == 3) {                                     // first pass: all gated correspondences are counted
         const double want = ceil(a.trim_frac * (double)total);
         k = want < 1.0 ? 1u : (want > (double)total ? total : (uint32_t)want);
@@ -290,9 +291,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
       bool have_ok = false, last_failed = false;
       __syncthreads();
       if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; }
-      for (int i = tid; i < ns; i += kThreads) s.slots[i] = (uint16_t)kNoSlot;   // no warm start for a new seed
-      if constexpr (kTrim) { for (int i = tid; i < ns; i += kThreads) trim_keys[i] = kNoSlot; }
-      for (int w = tid; w <= (ns - 1) >> 5 && ns > 0; w += kThreads) s.tiebits[w] = 0u;
+      if (model_ok && scene_ok && fits) {       // (a pair that does not fit must not touch the carved arrays: ns may exceed scap)
+        for (int i = tid; i < ns; i += kThreads) s.slots[i] = (uint16_t)kNoSlot;   // no warm start for a new seed
+        if constexpr (kTrim) { for (int i = tid; i < ns; i += kThreads) trim_keys[i] = kNoSlot; }
+        for (int w = tid; w <= (ns - 1) >> 5 && ns > 0; w += kThreads) s.tiebits[w] = 0u;
+      }
       __syncthreads();
 
       if (!model_ok) status |= CCICP_ST_TOO_FEW_MODEL;
@@ -392,7 +395,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
           }
           if (last_delta < a.min_delta) { status |= CCICP_ST_CONVERGED; break; }
         }
-        if (!have_ok) status |= CCICP_ST_NO_CORR;
+        if (!have_ok && iters > 0) status |= CCICP_ST_NO_CORR;   // max_iter <= 0: no fitStep ran, the reference reports nothing
       }
 
       // ---- outputs: correspondences of the last executed iteration
@@ -401,7 +404,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
         int32_t* dst = a.corr_idx + (size_t)seed * (size_t)a.total_scene + s0;
         for (int i = tid; i < ns; i += kThreads) {
           int32_t o = -1;
-          if (model_ok && scene_ok && iters > 0) {
+          if (model_ok && scene_ok && fits && iters > 0) {
             const unsigned slot = s.slots[i];
             if (slot != kNoSlot) o = s.morig[slot];
           }

@@ -42,3 +42,40 @@ def gpu_lockstep_corr(ctx, pair, Rt_trace, indist=5.0, flags=0):
     prm = capi.default_params(max_iter=1, min_delta=-2.0, indist=indist, flags=flags)
     res, corr = ctx.register_batch(mxy, moff, sxy, soff, np.asarray(Rt_trace), prm, n_seeds=k, want_corr=True)
     return corr, res
+
+
+# ---- the oracle over many problems, forked over the host cores (the reference is not thread-safe:
+# matrix.cpp:26-31 file-static scratch; one PROCESS per core like bench.py's CPU arm) -------------------------
+def _oracle_job(job):
+    from oracle import refbind
+    (pair, Rt0, kw), opts = job
+    tr = refbind.trace(*pair, Rt0, want_tie=False, **kw)
+    out = dict(iters=tr["iters"], status=tr["status"], Rt=tr["Rt"])
+    ok = np.nonzero(tr["ncorr"] > 0)[0]
+    if len(ok):                      # numCorr / cModelPoints of the reference: the last fitStep that had correspondences
+        k = ok[-1]
+        out["num_corr"] = int(tr["ncorr"][k])
+        out["score"] = float(tr["dis"][k][tr["corr"][k] >= 0].astype(np.float64).mean())
+    else:
+        out["num_corr"], out["score"] = 0, float("inf")
+    if opts.get("last_corr"):
+        out["corr"] = tr["corr"][-1].copy() if tr["iters"] else np.zeros(0, np.int32)
+    if opts.get("all_corr"):
+        out["corr"] = tr["corr"].copy()
+    return out
+
+
+def oracle_map(jobs, **opts):
+    """jobs: list of (pair, Rt0, trace kwargs).  Returns one small dict per job (see _oracle_job)."""
+    import multiprocessing as mp
+    import os
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    jobs = [(j, opts) for j in jobs]
+    if cores <= 1 or len(jobs) < 4:
+        return [_oracle_job(j) for j in jobs]
+    # fork: the children only run the CPU oracle (never CUDA) and leave through os._exit
+    with mp.get_context("fork").Pool(min(cores, 32)) as pool:
+        return pool.map(_oracle_job, jobs, chunksize=max(1, len(jobs) // (cores * 8)))
