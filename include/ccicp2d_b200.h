@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CCICP_ABI_VERSION 3
+#define CCICP_ABI_VERSION 4
 
 /* ---- call-level error codes ------------------------------------------- */
 enum {
@@ -53,7 +53,11 @@ enum {
   CCICP_ST_NO_CORR       = 1u << 2, /* no iteration produced a correspondence (fitStep -1, icpPointToPoint.cpp:128-131)        */
   CCICP_ST_REFLECTION    = 1u << 3, /* some iteration had det(H) < 0; like the reference (no det fix, icpPointToPoint.cpp:162)
                                        the improper V*U^T was applied                                                         */
-  CCICP_ST_DEGENERATE    = 1u << 4, /* some iteration had a rank-deficient H (det == 0); result not comparable                 */
+  CCICP_ST_DEGENERATE    = 1u << 4, /* some iteration had a (nearly) rank-deficient H: |det H| <= 1e-9 ||H||_F^2 (one or two
+                                       correspondences, collinear ones).  There the reference's SVD (matrix.cpp:582-810) and the
+                                       default closed form pick their factor differently, so the library re-runs such a problem
+                                       with the exact-order solve (CCICP_ST_EXACT_RETRY); the bit survives only where that
+                                       re-run met det H == 0 exactly or the re-run is disabled (CCICP_F_NO_EXACT_RETRY)          */
   CCICP_ST_TIE_REPLAY    = 1u << 5, /* >= 1 query had several model points at the same float distance and was resolved by
                                        replaying the reference kd-tree traversal (kdtree.cpp:515-683)                          */
   CCICP_ST_CONVERGED     = 1u << 6, /* stopped because delta < min_delta (icp.cpp:119-120)                                     */
@@ -63,6 +67,8 @@ enum {
   CCICP_ST_NO_SEED_BELOW = 1u << 10, /* CCICP_F_FIRST_BELOW: no seed reached score / n_scene < score_threshold; the record is the
                                        arg-min seed instead (global_match.cpp:151-174 publishes nothing in that case)           */
   CCICP_ST_EDGE_REJECTED = 1u << 11, /* ccicp_match_batch with reject_dist > 0: the result moved too far from the initial pose     */
+  CCICP_ST_EXACT_RETRY   = 1u << 12, /* this record comes from the exact-order re-run of a problem whose default-mode solve was
+                                       flagged CCICP_ST_DEGENERATE: R,t bit-identical to the reference                          */
   CCICP_ST_HINT_TOO_SMALL = 1u << 9 /* max_cells_hint of ccicp_register_batch_device_ex was too small for this pair: not
                                        registered, R,t returned unchanged                                                      */
 };
@@ -78,6 +84,10 @@ enum {
   CCICP_F_TRIM           = 1u << 6, /* north_star extra, NO counterpart in the reference (its only outlier test is the fixed
                                        gate, icpPointToPoint.cpp:76,111): trimmed rejection, keep the params.trim_frac
                                        fraction of the gated correspondences per iteration.  Off in every parity run. */
+  CCICP_F_DIAG_COUNTS    = 1u << 7, /* diagnostics only: run the counting instantiation of the pair kernel (same algorithm and
+                                       results, slower) and accumulate the work it did; read with ccicp_get_diag_counts.  Never
+                                       set in a timed run.                                                                     */
+  CCICP_F_NO_EXACT_RETRY = 1u << 8, /* diagnostics only: keep the default-mode record of problems flagged CCICP_ST_DEGENERATE    */
   CCICP_F_NO_TIE_REPLAY  = 1u << 3, /* diagnostics only: skip the kd-tree tie replay (ties -> lowest grid slot)                 */
   CCICP_F_EXACT_SUMS     = 1u << 4  /* evaluate centroids, H, the SVD (Matrix::svd, matrix.cpp:582-810) and the compose step in
                                        the reference's own sequential order: R,t of every iteration are then BIT-IDENTICAL to
@@ -250,6 +260,44 @@ int ccicp_edge_information_lum(ccicp_ctx* ctx, int32_t n_edges, const float* sou
 int32_t ccicp_knn_candidates(const double* nodes_xy, int32_t n_nodes, const double* query_xy, int32_t query_idx,
                              int32_t K, int32_t* out);
 
+/* ---- multi-device: the batch split over several GPUs of one process ---------------------------------------------
+ * north_star: "the batch is sharded across the 8 GPUs of one box with only a final NCCL gather of transforms, since
+ * pairs are independent".  The reference has no counterpart (single-threaded CPU); the consumer of such a call is
+ * graph_slam's loop-closure candidate producer: graphSlamGetKNN (graph_slam/src/graphSlamTools.cpp:72-106) proposes the
+ * candidate pairs, graphSlamAddEdgeToX (:406-425) registers each (the ICP call at :274).
+ * Device g of G registers the contiguous pair range ccicp_shard_range(n_pairs, G, g) with its own ctx, driven by its
+ * own host thread inside the calling process; there is no data-path collective.
+ *   devices: CUDA device indices (a device may be listed twice: two ctxs share it); NULL, 0 = every visible device. */
+typedef struct ccicp_multi ccicp_multi;
+int  ccicp_multi_create(const int* devices, int n_devices, ccicp_multi** out);
+int  ccicp_multi_destroy(ccicp_multi* m);
+int  ccicp_multi_device_count(const ccicp_multi* m);
+ccicp_ctx* ccicp_multi_ctx(ccicp_multi* m, int g);            /* the ctx of device slot g (launch info, errors)     */
+const char* ccicp_multi_last_error(const ccicp_multi* m);
+void ccicp_shard_range(int32_t n_pairs, int n_devices, int g, int32_t* begin, int32_t* end);  /* contiguous, balanced:
+                                             sizes differ by at most one, larger shards first */
+/* Host buffers: same arguments and result layout as ccicp_register_batch; every shard's records are copied straight
+ * into the caller's out[] (that is the gather on this path).  corr_idx only with n_seeds == 1.  Synchronous.        */
+int ccicp_register_batch_multi(ccicp_multi* m, int32_t n_pairs, int32_t n_seeds,
+                               const double* model_xy, const int32_t* model_off,
+                               const double* scene_xy, const int32_t* scene_off,
+                               const double* init_Rt, const ccicp_params* params,
+                               ccicp_result* out, int32_t* corr_idx);
+/* Device-resident shards: every argument is an array with one entry per device slot.  Device g holds ITS shard as a CSR
+ * of its own (offsets from 0; d_init_Rt[g] = the shard's transforms) and a record buffer d_out[g] sized for ALL n_pairs
+ * (x n_seeds unless best-of) records.  Each device registers its shard into its slice of d_out[g]; the slices are then
+ * exchanged so that EVERY d_out[g] holds every record: over NCCL (one grouped ncclBroadcast per shard over
+ * NVLink/NVSwitch; libnccl.so.2 is bound at run time) or, when NCCL is unavailable or a device is listed twice, by peer
+ * copies (ccicp_multi_gather_kind: 1 = NCCL, 2 = peer copies).  Asynchronous; ccicp_multi_sync waits for all devices. */
+int ccicp_register_batch_multi_device(ccicp_multi* m, int32_t n_pairs, int32_t n_seeds,
+                                      const double* const* d_model_xy, const int32_t* const* d_model_off,
+                                      const double* const* d_scene_xy, const int32_t* const* d_scene_off,
+                                      const double* const* d_init_Rt, const ccicp_params* params,
+                                      ccicp_result* const* d_out, const int32_t* max_model, const int32_t* max_scene,
+                                      const int32_t* max_cells_hint /* may be NULL */);
+int ccicp_multi_sync(ccicp_multi* m);
+int ccicp_multi_gather_kind(const ccicp_multi* m);
+
 /* Pinned host memory for callers that want the H2D/D2H copies to overlap. */
 int ccicp_host_alloc(void** out, size_t bytes);
 int ccicp_host_free(void* p);
@@ -264,6 +312,10 @@ typedef struct ccicp_launch_info {
   float   last_h2d_ms, last_d2h_ms;
 } ccicp_launch_info;
 int ccicp_get_launch_info(ccicp_ctx* ctx, ccicp_launch_info* out);
+/* Work counted by the CCICP_F_DIAG_COUNTS launches since the last call (then reset), synchronises the ctx streams:
+ * out[0] = float distance evaluations of the NN search, out[1] = NN queries searched, out[2] = accepted (gated)
+ * correspondences summed over the iterations.  The "useful work" of bench.py's roofline_useful comes from these. */
+int ccicp_get_diag_counts(ccicp_ctx* ctx, uint64_t out[3]);
 
 #ifdef __cplusplus
 }

@@ -1,10 +1,11 @@
 """TEST INFRASTRUCTURE (oracle): CPU restatement of CCICP::classifyPoints
 (ccicp2d/src/icpTools.cpp:36-103; NUMBINSGA 1200, RESOLUTION 0.5, GRD_ADJ_THRESH 2: icpTools.h:24-26).
 
-PARITY UNPINNED: the reference function lives in icpTools.cpp, which needs PCL / tf / Eigen headers that are not in
-this image, so it cannot be compiled here and the reference has no test vectors for it.  Two
-independent restatements are kept and checked against each other: `classify_literal` follows the reference loop by
-loop (bins as Python lists), `classify` is the vectorised form used for larger clouds.
+PINNED: oracle/Makefile cuts the function (lines 36-103) out of the reference file at build time and compiles it
+unmodified against a small pcl::PointCloud shim (oracle/shim_pcl/classify_shim.h) into oracle/_ref/libclassify_ref.so;
+tests/test_classify_cpu.py checks this port against it (order, coordinates, flags).  The port stays because it also
+returns the source index of every kept point, which the reference does not carry, and as the fallback where the
+compiled library is absent.  `classify_literal` follows the reference loop by loop, `classify` is the vectorised form.
 Only tests/, __graft_entry__.smoke() and bench.py's CPU leg may import this module."""
 import math
 

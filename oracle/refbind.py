@@ -15,6 +15,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REF_PATH = os.path.join(_HERE, "_ref", "libccicp_ref.so")
 PORT_PATH = os.path.join(_HERE, "libccicp_port.so")
+CLASSIFY_REF_PATH = os.path.join(_HERE, "_ref", "libclassify_ref.so")
 
 OK, TOO_FEW_MODEL, TOO_FEW_SCENE, NO_CORR = 0, 1, 2, 4
 _libs = {}
@@ -113,3 +114,23 @@ def nn(pts, q, kind=None):
     dis = np.zeros(len(q), np.float32)
     f(_p(pts), len(pts), _p(q), len(q), _p(idx), _p(dis))
     return idx, dis
+
+
+def classify_available():
+    return os.path.exists(CLASSIFY_REF_PATH)
+
+
+def classify_ref(xyz):
+    """The reference's own CCICP::classifyPoints (icpTools.cpp:36-103, compiled unmodified: oracle/Makefile).
+    xyz float32 [n,3], finite coordinates only.  Returns (xyz_out [k,3], ground_adj [k])."""
+    if "classify" not in _libs:
+        lib = C.CDLL(CLASSIFY_REF_PATH)
+        lib.ccref_classify.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        lib.ccref_classify.restype = C.c_int
+        _libs["classify"] = lib
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    n = len(xyz)
+    out = np.zeros((max(n, 1), 3), np.float32)
+    ga = np.zeros(max(n, 1), np.uint8)
+    k = _libs["classify"].ccref_classify(_p(xyz), n, _p(out), _p(ga))
+    return out[:k].copy(), ga[:k].copy()

@@ -57,7 +57,10 @@ def build_cuda(force=False, verbose=False, extra=()):
     out = os.path.join(LIB, "libccicp2d_b200.so")
     srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", "ccicp2d_b200.h"), __file__]
     if force or _newer(out, srcs):
-        _run([nvcc_path()] + NVCC_FLAGS + list(extra) + ["-o", out, os.path.join(CSRC, "ccicp_api.cu")], verbose)
+        tmp = out + ".tmp"              # the library is replaced in one rename: a snapshot never sees a half-written file
+        _run([nvcc_path()] + NVCC_FLAGS + list(extra) + ["-o", tmp, os.path.join(CSRC, "ccicp_api.cu"),
+                                                       os.path.join(CSRC, "ccicp_multi.cu"), "-ldl"], verbose)
+        os.replace(tmp, out)
     return out
 
 
@@ -89,6 +92,11 @@ def build_host_tests(force=False, verbose=False):
     srcs = [os.path.join(d, "kdreplay_host.cpp"), os.path.join(CSRC, "kdreplay.h")]
     if force or _newer(out, srcs):
         _run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", out, srcs[0]], verbose)
+    # host build of the grid search (nn_grid.h) for the CPU exactness test
+    out2 = os.path.join(d, "libnn_grid_host.so")
+    srcs2 = [os.path.join(d, "nn_grid_host.cpp"), os.path.join(CSRC, "nn_grid.h")]
+    if force or _newer(out2, srcs2):
+        _run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", out2, srcs2[0]], verbose)
     return out
 
 
@@ -108,6 +116,12 @@ def build_callsite(force=False, verbose=False):
     if force or _newer(out2, [src2, hdr2, os.path.join(ROOT, "include", "ccicp2d_b200.h"), os.path.join(LIB, "libccicp2d_b200.so")]):
         _run(["g++", "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(ROOT, "include"), "-o", out2, src2, "-L" + LIB,
               "-lccicp2d_b200", "-Wl,-rpath,$ORIGIN/../../slam_b200/lib"], verbose)
+    # a C++ host driving several GPUs through the multi-device entry points (no Python, no torch)
+    out3, src3 = os.path.join(d, "multi_demo_b200"), os.path.join(d, "multi_demo.cu")
+    if os.path.exists(src3) and (force or _newer(out3, [src3, os.path.join(ROOT, "include", "ccicp2d_b200.h"),
+                                                        os.path.join(LIB, "libccicp2d_b200.so"), os.path.join(LIB, "libscangen.so")])):
+        _run([nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-O2", "-std=c++17", "-o", out3, src3, "-L" + LIB,
+              "-lccicp2d_b200", "-lscangen", "-Xlinker", "-rpath=$ORIGIN/../../slam_b200/lib"], verbose)
     return out
 
 

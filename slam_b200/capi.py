@@ -17,8 +17,9 @@ LIB_PATH = os.environ.get("CCICP_LIB") or os.path.join(_HERE, "lib", "libccicp2d
 OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
 ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
 ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
-ST_NO_SEED_BELOW, ST_EDGE_REJECTED = 1024, 2048
+ST_NO_SEED_BELOW, ST_EDGE_REJECTED, ST_EXACT_RETRY = 1024, 2048, 4096
 F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW, F_TRIM = 1, 2, 4, 8, 16, 32, 64
+F_DIAG_COUNTS, F_NO_EXACT_RETRY = 128, 256
 
 
 class Params(C.Structure):
@@ -43,7 +44,10 @@ SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror
            "ccicp_default_params", "ccicp_register_batch", "ccicp_register_batch_device", "ccicp_stream_sync",
            "ccicp_host_alloc", "ccicp_host_free", "ccicp_get_launch_info", "ccicp_match_batch", "ccicp_pose_to_rt",
            "ccicp_rt_to_pose", "ccicp_classify_points", "ccicp_classify_points_device", "ccicp_register_batch_device_ex",
-           "ccicp_grid_cells", "ccicp_edge_information_lum", "ccicp_knn_candidates"]
+           "ccicp_grid_cells", "ccicp_edge_information_lum", "ccicp_knn_candidates", "ccicp_get_diag_counts",
+           "ccicp_multi_create", "ccicp_multi_destroy", "ccicp_multi_device_count", "ccicp_multi_ctx", "ccicp_multi_last_error",
+           "ccicp_shard_range", "ccicp_register_batch_multi", "ccicp_register_batch_multi_device", "ccicp_multi_sync",
+           "ccicp_multi_gather_kind"]
 
 _lib = None
 
@@ -84,6 +88,7 @@ def load():
     lib.ccicp_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     lib.ccicp_host_free.argtypes = [vp]
     lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
+    lib.ccicp_get_diag_counts.argtypes = [vp, vp]
     lib.ccicp_match_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
     lib.ccicp_classify_points.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     lib.ccicp_classify_points_device.argtypes = [vp, i32, vp, vp, C.c_int64, vp, vp, vp, vp, vp]
@@ -220,6 +225,12 @@ class Context:
 
     def sync(self, stream=None):
         self._check(self.lib.ccicp_stream_sync(self.h, stream or None))
+
+    def diag_counts(self):
+        """(distance evaluations, queries searched, accepted pairs) of the F_DIAG_COUNTS launches since the last call."""
+        out = np.zeros(3, np.uint64)
+        self._check(self.lib.ccicp_get_diag_counts(self.h, _ptr(out)))
+        return int(out[0]), int(out[1]), int(out[2])
 
     def launch_info(self):
         li = LaunchInfo()

@@ -36,7 +36,7 @@ struct ccicp_ctx {
   int stage_kb = 200;         // CCICP_STAGE_KB
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the L2 variant
   void* timed_stream = nullptr;
-  DevBuf counter, scratch, all_results, workspace;
+  DevBuf counter, scratch, all_results, workspace, diag, retry_list;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
   DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap, c_tile_base, c_tile_seg, c_group_base;            // classification scratch
   DevBuf l_src, l_soff, l_tgt, l_toff, l_dist, l_idx, l_info, l_num, l_status;   // Lu-Milios edge information
@@ -122,11 +122,20 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   // on-chip variant when the pair's working set fits the SM's shared memory, else the L2 variant
   const bool exact = (prm->flags & CCICP_F_EXACT_SUMS) != 0;
   const bool trim = (prm->flags & CCICP_F_TRIM) != 0;
+  const bool diag = (prm->flags & CCICP_F_DIAG_COUNTS) != 0;
   if (trim && (exact || !(prm->trim_frac > 0.0) || prm->trim_frac > 1.0)) return CCICP_E_INVALID;
-  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : icp_pair_kernel;
-  auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : icp_pair_l2_kernel;
+  if (diag && (exact || trim)) return CCICP_E_INVALID;
+  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : diag ? icp_pair_diag_kernel : icp_pair_kernel;
+  auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : diag ? icp_pair_l2_diag_kernel : icp_pair_l2_kernel;
   cudaFuncAttributes fa_on;
   CK(cudaFuncGetAttributes(&fa_on, k_on));
+  // problems whose default-mode solve meets a (nearly) rank-deficient H are re-run by the exact-order instantiation
+  const bool retry = !exact && !trim && !diag && !(prm->flags & CCICP_F_NO_EXACT_RETRY);
+  if (retry) {
+    cudaFuncAttributes fa_ex;
+    CK(cudaFuncGetAttributes(&fa_ex, icp_pair_exact_kernel));
+    if (fa_ex.sharedSizeBytes > fa_on.sharedSizeBytes) fa_on.sharedSizeBytes = fa_ex.sharedSizeBytes;
+  }
   // CCICP_F_TRIM: one u32 per scene point behind the carved working set (this iteration's squared distances, the keys
   // of the radix select)
   const size_t warm_bytes = trim ? align_up((size_t)a.scap * 4, 128) : 0;
@@ -170,7 +179,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     kernel_out = (ccicp_result*)ctx->all_results.p;
   }
   // `slot` separates launches that may be in flight together (chunked host path): own work counter, own scratch
-  int rc = reserve(ctx, ctx->counter, 256);
+  int rc = reserve(ctx, ctx->counter, 16 * 16);
   if (rc) return rc;
   const size_t per_cta = replay_scratch_bytes(max_model);
   const size_t per_slot = per_cta * (size_t)resident;
@@ -192,20 +201,59 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   }
   a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
   a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
-  a.work_counter = (int32_t*)ctx->counter.p + (slot & 15);
+  int32_t* cnt = (int32_t*)ctx->counter.p + 4 * (slot & 15);      // {work, retry work, retry count, -} of this slot
+  a.work_counter = cnt;
   a.scratch = (char*)ctx->scratch.p + (size_t)(slot % n_slots) * per_slot; a.scratch_per_cta = per_cta;
   a.pair_base = pair_base;
   a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
   a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
   a.trim_frac = prm->trim_frac;
   a.total_scene = total_scene; a.max_model = max_model;
+  if (diag) {
+    const bool fresh = ctx->diag.p == nullptr;
+    rc = reserve(ctx, ctx->diag, 32);
+    if (rc) return rc;
+    if (fresh) CK(cudaMemsetAsync(ctx->diag.p, 0, 32, st));
+    a.diag = (unsigned long long*)ctx->diag.p;
+  }
 
-  CK(cudaMemsetAsync(a.work_counter, 0, 4, st));
+  CK(cudaMemsetAsync(cnt, 0, 16, st));
   if (slot == 0) CK(cudaEventRecord(ctx->ev[2], st));
   if (use_l2) k_l2<<<grid, threads, smem, st>>>(a);
   else k_on<<<grid, threads, smem, st>>>(a);
   CK(cudaGetLastError());
   ctx->info.n_launches += 1;
+  if (retry) {
+    const size_t first = (size_t)pair_base * n_seeds, n_prob = (size_t)n_pairs * n_seeds;
+    if (ctx->retry_list.cap < (first + n_prob) * 4) {
+      if (slot != 0) return CCICP_E_INVALID;      // the host-buffer call reserves the whole batch up front
+      rc = reserve(ctx, ctx->retry_list, (first + n_prob) * 4);
+      if (rc) return rc;
+    }
+    int32_t* list = (int32_t*)ctx->retry_list.p + first;
+    collect_retry_kernel<<<(unsigned)((n_prob + 255) / 256), 256, 0, st>>>(kernel_out, (int)first, (int)n_prob, list, cnt + 2);
+    CK(cudaGetLastError());
+    IcpArgs a2 = a;
+    a2.item_list = list; a2.item_count = cnt + 2; a2.work_counter = cnt + 1;
+    auto k2_on = icp_pair_exact_kernel;
+    auto k2_l2 = icp_pair_l2_exact_kernel;
+    int occ2 = 0;
+    if (use_l2) {
+      CK(cudaFuncSetAttribute(k2_l2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, k2_l2, threads, smem));
+    } else {
+      CK(cudaFuncSetAttribute(k2_on, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, k2_on, threads, smem));
+    }
+    if (occ2 < 1) return CCICP_E_TOO_LARGE;
+    if (occ2 > occ) occ2 = occ;                   // the scratch and the L2 workspace are sized for `resident` CTAs
+    const long long res2 = (long long)occ2 * ctx->sm_count;
+    const int grid2 = (int)((long long)n_prob < res2 ? (long long)n_prob : res2);
+    if (use_l2) k2_l2<<<grid2, threads, smem, st>>>(a2);
+    else k2_on<<<grid2, threads, smem, st>>>(a2);
+    CK(cudaGetLastError());
+    ctx->info.n_launches += 2;
+  }
   if (best_of) {
     const int threads = 128, warps_per_block = threads / 32;
     select_best_seed_kernel<<<(n_pairs + warps_per_block - 1) / warps_per_block, threads, 0, st>>>(
@@ -301,7 +349,7 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   if (!ctx) return CCICP_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
+  DevBuf* bufs[] = {&ctx->retry_list, &ctx->diag, &ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
                     &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_tile_base, &ctx->c_tile_seg, &ctx->c_group_base, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
                     &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
@@ -394,6 +442,7 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   if ((rc = reserve(ctx, ctx->d_init, n_prob * 48))) return rc;
   if ((rc = reserve(ctx, ctx->d_out, n_out * sizeof(ccicp_result)))) return rc;
   if (corr_idx && (rc = reserve(ctx, ctx->d_corr, (size_t)n_scene * n_seeds * 4 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->retry_list, n_prob * 4 + 16))) return rc;
 
   // Chunked pipeline: the H2D copy of chunk c+1 (copy stream) overlaps the kernel of chunk c; consecutive
   // chunks run on two compute streams so the tail of one kernel overlaps the head of the next.  The offsets
@@ -656,6 +705,19 @@ int ccicp_host_free(void* p) {
   if (!p) return CCICP_OK;
   cudaError_t e = cudaFreeHost(p);
   if (e != cudaSuccess) { cudaGetLastError(); return CCICP_E_CUDA; }
+  return CCICP_OK;
+}
+
+int ccicp_get_diag_counts(ccicp_ctx* ctx, uint64_t out[3]) {
+  if (!ctx || !out) return CCICP_E_INVALID;
+  out[0] = out[1] = out[2] = 0;
+  if (!ctx->diag.p) return CCICP_OK;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaDeviceSynchronize());
+  unsigned long long h[4] = {0, 0, 0, 0};
+  CK(cudaMemcpy(h, ctx->diag.p, 32, cudaMemcpyDeviceToHost));
+  CK(cudaMemset(ctx->diag.p, 0, 32));
+  out[0] = h[0]; out[1] = h[1]; out[2] = h[2];
   return CCICP_OK;
 }
 

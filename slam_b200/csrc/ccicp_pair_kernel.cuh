@@ -132,9 +132,8 @@ __device__ __forceinline__ void build_grid(const IcpArgs& a, const Smem& s, int 
     const GridP& g = s.grid[i >= nGA];
     if (g.G == 0) continue;
     float2 f = tmp_pts[i];
-    int ix = (int)__fmul_rn(__fsub_rn(f.x, g.minx), g.inv_h);
-    int iy = (int)__fmul_rn(__fsub_rn(f.y, g.miny), g.inv_h);
-    ix = min(max(ix, 0), g.G - 1); iy = min(max(iy, 0), g.G - 1);
+    int ix, iy;
+    cell_of(g, f.x, f.y, ix, iy);
     const int cell = g.base + iy * g.G + ix;
     const int sh = (cell & 1) * 16;
     uint32_t old = atomicAdd(&cnt32[cell >> 1], 1u << sh);
@@ -266,7 +265,7 @@ __device__ __forceinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s
     CtaCoop<kThreads> co;
     co.tid = tid; co.nt = kThreads; co.cap = stage_cap;
     co.sv = (float*)stage; co.si = (uint16_t*)(stage + (size_t)stage_cap * 4);
-    co.bcast = &s.misc[15]; co.fred = fred;
+    co.bcast = &s.misc[M_BCAST]; co.fred = fred;
     co.rank = (rank_base ? rank_base
                          : (uint16_t*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta + replay_nodes_bytes(a.max_model))) + g.first;
     int* nn = &s.misc[M_NNODE + cls];

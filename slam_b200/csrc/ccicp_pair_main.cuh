@@ -27,17 +27,67 @@ __device__ __forceinline__ void block_reduce(double* red, int off, double (&v)[N
   }
 }
 
+// Sum of 8 doubles per lane over the warp by a halving butterfly: after the xor-16 / 8 / 4 rounds every lane carries
+// ONE of the 8 values (4 + 2 + 1 exchanges instead of 8 x 5), two plain rounds finish it.  Returns the warp total of
+// value index lane >> 2 (valid in every lane; lanes with (lane & 3) == 0 publish it).  Fixed order: deterministic.
+__device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
+  const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0, h4 = (lane & 4) != 0;
+  double a[4], b[2];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const double keep = h16 ? v[k + 4] : v[k], send = h16 ? v[k] : v[k + 4];
+    a[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const double keep = h8 ? a[k + 2] : a[k], send = h8 ? a[k] : a[k + 2];
+    b[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+  const double keep = h4 ? b[1] : b[0], send = h4 ? b[0] : b[1];
+  double c = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  c += __shfl_xor_sync(0xffffffffu, c, 2);
+  c += __shfl_xor_sync(0xffffffffu, c, 1);
+  return c;
+}
+
+// Every warp publishes its partial sums (8 doubles) and its count of accepted pairs; ONE warp then adds the partials in
+// warp order and solves (solve_warp0), so the FP64 tail of an iteration is issued once per CTA, not once per warp.
+__device__ __forceinline__ void publish_partials(double* red, const double (&v)[8], int cnt, int tid) {
+  const int lane = tid & 31;
+  const double c = warp_sum8(v, lane);
+  const int wc = __reduce_add_sync(0xffffffffu, cnt);
+  double* r = red + (tid >> 5) * kRedStride;
+  if ((lane & 3) == 0) r[lane >> 2] = c;
+  if (lane == 0) ((int*)&r[8])[0] = wc;
+}
+
+// warp 0, after the barrier: total count n and the 8 totals (in every lane)
+template <int kWarps>
+__device__ __forceinline__ int gather_partials(const double* red, double (&v)[8], int lane) {
+  const int n = __reduce_add_sync(0xffffffffu, lane < kWarps ? ((const int*)&red[lane * kRedStride + 8])[0] : 0);
+  double t = 0.0;
+#pragma unroll
+  for (int w = 0; w < kWarps; w++) t += red[w * kRedStride + (lane & 7)];
+#pragma unroll
+  for (int k = 0; k < 8; k++) v[k] = __shfl_sync(0xffffffffu, t, k);
+  return n;
+}
+
 // a8 + a9.  Closed form of R_ = V*U^T for the 2x2 H = sum q_t^T q_m
 // (icpPointToPoint.cpp:159-163): a rotation when det H > 0, the improper
 // (reflection) polar factor when det H < 0 -- the reference applies no det fix.
 __device__ __forceinline__ double solve_and_compose(const double* H, const double* mu_m, const double* mu_t,
                                                     double* Rt, uint32_t& status) {
   const double det = H[0] * H[3] - H[1] * H[2];
+  // Rank-deficient or nearly so (one or two correspondences, collinear ones): the sign of det H is rounding noise and
+  // the reference's SVD picks its factor by its own internals, so the closed form is not comparable here.  Flagged;
+  // the host side re-runs flagged problems with the exact-order instantiation (see launch_icp).
+  if (fabs(det) <= 1e-9 * (H[0] * H[0] + H[1] * H[1] + H[2] * H[2] + H[3] * H[3])) status |= CCICP_ST_DEGENERATE;
   double r00, r01, r10, r11;
   if (det >= 0.0) {
     const double A = H[0] + H[3], B = H[1] - H[2];
     const double r = sqrt(A * A + B * B);
-    if (det == 0.0 || !(r > 0.0)) status |= CCICP_ST_DEGENERATE;
+    if (!(r > 0.0)) status |= CCICP_ST_DEGENERATE;
     const double c = r > 0.0 ? A / r : 1.0, s = r > 0.0 ? B / r : 0.0;
     r00 = c; r01 = -s; r10 = s; r11 = c;
   } else {
@@ -228,7 +278,7 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double
   }
 }
 
-template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false>
+template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false, bool kDiag = false>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
@@ -236,7 +286,8 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   __shared__ double rtprev_s[8 + kWarps * 4];     // + float[kWarps][8] min/max / scan scratch of the tie replay
   __shared__ double exact_s[kExact ? 16 : 1];
   __shared__ GridP grid_s[2];
-  __shared__ int misc_s[16];
+  __shared__ int misc_s[M_COUNT];
+  __shared__ double sol_s[8];          // warp 0 -> CTA: new R,t, delta, {n, status bits} of the iteration
   __shared__ uint32_t trim_s[kTrim ? 260 : 1];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
   Smem s = carve<kGlobal>(base, a.mcap, a.scap, a.ccap, red_s, rtprev_s, grid_s, misc_s);
@@ -248,7 +299,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   const int tid = threadIdx.x;
   const float gate_f = __double2float_ru(a.indist);
   const bool replay_on = !(a.flags & CCICP_F_NO_TIE_REPLAY);
-  const int n_items = a.n_pairs * a.items_per_pair;
+  // a.item_list (exact-order re-run of flagged problems): one listed (pair, seed) problem per work item, the count
+  // was left on the device by collect_retry_kernel
+  const bool listed = a.item_list != nullptr;
+  const int n_items = listed ? *a.item_count : a.n_pairs * a.items_per_pair;
+  int diag_evals = 0, diag_queries = 0, diag_inliers = 0;      // kDiag only (dead otherwise)
 
   for (;;) {
     __syncthreads();
@@ -256,9 +311,15 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
     __syncthreads();
     const int item = s.misc[M_WORK];
     if (item >= n_items) break;
-    const int pair = a.pair_base + item / a.items_per_pair;
-    const int seed0 = (item % a.items_per_pair) * a.seeds_per_item;
-    const int seed1 = min(seed0 + a.seeds_per_item, a.n_seeds);
+    int pair, seed0, seed1;
+    if (listed) {
+      const int prob = a.item_list[item];
+      pair = prob / a.n_seeds; seed0 = prob - pair * a.n_seeds; seed1 = seed0 + 1;
+    } else {
+      pair = a.pair_base + item / a.items_per_pair;
+      seed0 = (item % a.items_per_pair) * a.seeds_per_item;
+      seed1 = min(seed0 + a.seeds_per_item, a.n_seeds);
+    }
 
     const int m0 = a.model_off[2 * pair], nmGA = a.model_off[2 * pair + 1] - m0, nmNGA = a.model_off[2 * pair + 2] - a.model_off[2 * pair + 1];
     const int s0 = a.scene_off[2 * pair], nsGA = a.scene_off[2 * pair + 1] - s0, nsNGA = a.scene_off[2 * pair + 2] - a.scene_off[2 * pair + 1];
@@ -285,12 +346,12 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
       double Rt[6];
 #pragma unroll
       for (int k = 0; k < 6; k++) Rt[k] = __ldg(a.init_Rt + prob * 6 + k);
-      uint32_t status = 0;
+      uint32_t status = listed ? (uint32_t)CCICP_ST_EXACT_RETRY : 0u;
       int iters = 0, num_corr = 0;
       double last_delta = 0.0;
       bool have_ok = false, last_failed = false;
       __syncthreads();
-      if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; }
+      if (tid == 0) { s.misc[M_REPLAYS] = 0; s.misc[M_TREEFAIL] = 0; s.misc[M_TIEFLAG] = 0; s.misc[M_TIEFLAG + 1] = 0; }
       if (model_ok && scene_ok && fits) {       // (a pair that does not fit must not touch the carved arrays: ns may exceed scap)
         for (int i = tid; i < ns; i += kThreads) s.slots[i] = (uint16_t)kNoSlot;   // no warm start for a new seed
         if constexpr (kTrim) { for (int i = tid; i < ns; i += kThreads) trim_keys[i] = kNoSlot; }
@@ -305,8 +366,8 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
         const GridP& gp = s.grid[nmNGA >= nmGA];
         const double pcx = (double)gp.cx, pcy = (double)gp.cy;     // pivot of the shifted sums
         for (int iter = 0; iter < a.max_iter; iter++) {
-          double* red = s.red + (iter & 1) * (kWarps * kRedStride);
-          // ---- a4..a6: transform, nearest neighbour, gate; shifted sums of the accepted pairs
+          const int par = iter & 1;
+          // ---- a4..a6: transform, nearest neighbour, gate
           int pend = 0;
           for (int i = tid; i < ns; i += kThreads) {          // loop A: search only (few live registers)
             const double2 sp = s.scene[i];
@@ -318,7 +379,8 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               float best; int bslot, tie;
               unsigned start = s.slots[i];
               if constexpr (kTrim) { if (start == kNoSlot) start = trim_keys[i] & 0xFFFFu; }
-              nn_search<kGlobal>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie);
+              nn_search<kGlobal, kDiag>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
+              if (kDiag) diag_queries++;
               if (bslot >= 0 && (double)best < a.indist) {
                 slot = (unsigned)bslot;
                 if (tie && replay_on) { pend = 1; atomicOr(&s.tiebits[i >> 5], 1u << (i & 31)); }
@@ -327,18 +389,15 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             s.slots[i] = (uint16_t)slot;
           }
           if constexpr (kTrim) trim_select<kThreads>(a, s, Rt, ns, tid, trim_s, trim_keys);
+          // ---- a7: shifted sums of the accepted pairs; every warp publishes its partials, warp 0 adds them and solves
           double v[8];
           int cnt;
           sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);        // loop B: converged accumulation
-          {
-            const int wc = __reduce_add_sync(0xffffffffu, cnt);
-            const int wt = __any_sync(0xffffffffu, pend != 0);
-            if ((tid & 31) == 0) { int* ip = (int*)&red[(tid >> 5) * 10 + 8]; ip[0] = wc; ip[1] = wt; }
-          }
-          block_reduce<8, kWarps>(red, 0, v, tid);
-          int n = 0, any_tie = 0;
-#pragma unroll
-          for (int w = 0; w < kWarps; w++) { const int* ip = (const int*)&red[w * 10 + 8]; n += ip[0]; any_tie |= ip[1]; }
+          publish_partials(s.red, v, cnt, tid);
+          if (__any_sync(0xffffffffu, pend != 0) && (tid & 31) == 0) s.misc[M_TIEFLAG + par] = 1;
+          __syncthreads();
+          const int any_tie = s.misc[M_TIEFLAG + par];
+          if (tid == 0) s.misc[M_TIEFLAG + (par ^ 1)] = 0;   // the next iteration's flag (last read one barrier pair ago)
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
             if (kGlobal) {
               replay_ties_coop<kThreads>(a, s, Rt, ns, nsGA, tid, smem_raw, a.stage_cap, (float*)rtprev_s + 16, s.scene, nullptr);
@@ -356,13 +415,46 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             }
             status |= CCICP_ST_TIE_REPLAY;
             sums_from_slots<kThreads>(s, Rt, ns, tid, pcx, pcy, v, cnt);
-            const int wc = __reduce_add_sync(0xffffffffu, cnt);
-            if ((tid & 31) == 0) { int* ip = (int*)&red[(tid >> 5) * 10 + 8]; ip[0] = wc; ip[1] = 0; }
-            block_reduce<8, kWarps>(red, 0, v, tid);
-            n = 0;
-#pragma unroll
-            for (int w = 0; w < kWarps; w++) n += ((const int*)&red[w * 10 + 8])[0];
+            publish_partials(s.red, v, cnt, tid);
+            __syncthreads();
           }
+          // ---- a7..a9 on ONE warp: totals, centroids, centred cross-covariance, solve, compose
+          if (tid < 32) {
+            const int n = gather_partials<kWarps>(s.red, v, tid);
+            uint32_t st = 0;
+            double delta = -1.0;
+            double Rn[6];
+#pragma unroll
+            for (int q = 0; q < 6; q++) Rn[q] = Rt[q];
+            if (n > 0) {
+              if constexpr (kExact) {
+                exact_step(s, Rt, ns, n, tid, exact_s);
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < 6; q++) Rn[q] = exact_s[8 + q];
+                delta = exact_s[14];
+                st = (uint32_t)exact_s[15];
+              } else {
+                const double dm0 = v[0] / (double)n, dm1 = v[1] / (double)n, dt0 = v[2] / (double)n, dt1 = v[3] / (double)n;
+                const double mu_m[2] = {pcx + dm0, pcy + dm1};
+                const double mu_t[2] = {pcx + dt0, pcy + dt1};
+                const double H[4] = {v[4] - v[2] * dm0, v[5] - v[2] * dm1, v[6] - v[3] * dm0, v[7] - v[3] * dm1};
+                delta = solve_and_compose(H, mu_m, mu_t, Rn, st);
+              }
+            }
+            if (tid == 0) {
+              if (n > 0) {
+#pragma unroll
+                for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];     // pre-update R,t of the last successful iteration
+              }
+#pragma unroll
+              for (int q = 0; q < 6; q++) sol_s[q] = Rn[q];
+              sol_s[6] = delta;
+              ((int*)&sol_s[7])[0] = n; ((uint32_t*)&sol_s[7])[1] = st;
+            }
+          }
+          __syncthreads();
+          const int n = ((const int*)&sol_s[7])[0];
           iters++;
           if (n == 0) {                          // fitStep returns -1 before touching R,t (icpPointToPoint.cpp:128-131)
             last_delta = -1.0; last_failed = true;
@@ -370,29 +462,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             break;
           }
           last_failed = false; have_ok = true; num_corr = n;
-          // ---- a7: centroids and centred cross-covariance from the shifted sums
-          const double inv_n = 1.0 / (double)n;
-          const double dm0 = v[0] / (double)n, dm1 = v[1] / (double)n, dt0 = v[2] / (double)n, dt1 = v[3] / (double)n;
-          const double mu_m[2] = {pcx + dm0, pcy + dm1};
-          const double mu_t[2] = {pcx + dt0, pcy + dt1};
-          (void)inv_n;
-          const double H[4] = {v[4] - v[2] * dm0, v[5] - v[2] * dm1, v[6] - v[3] * dm0, v[7] - v[3] * dm1};
-          if (tid == 0) {
 #pragma unroll
-            for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];
-          }
-          // ---- a8, a9
-          if constexpr (kExact) {
-            __syncthreads();                  // slots of this iteration are final and visible
-            exact_step(s, Rt, ns, n, tid, exact_s);
-            __syncthreads();
-#pragma unroll
-            for (int q = 0; q < 6; q++) Rt[q] = exact_s[8 + q];
-            last_delta = exact_s[14];
-            status |= (uint32_t)exact_s[15];
-          } else {
-            last_delta = solve_and_compose(H, mu_m, mu_t, Rt, status);
-          }
+          for (int q = 0; q < 6; q++) Rt[q] = sol_s[q];
+          last_delta = sol_s[6];
+          status |= ((const uint32_t*)&sol_s[7])[1];
+          if (kDiag) diag_inliers += (tid == 0) ? n : 0;
           if (last_delta < a.min_delta) { status |= CCICP_ST_CONVERGED; break; }
         }
         if (!have_ok && iters > 0) status |= CCICP_ST_NO_CORR;   // max_iter <= 0: no fitStep ran, the reference reports nothing
@@ -429,7 +503,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search<kGlobal>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie);
+              nn_search<kGlobal, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
             }
             s.slots[i] = (uint16_t)slot;
@@ -502,6 +576,12 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
       }
     }
   }
+  if constexpr (kDiag) {      // diagnostics instantiation: totals of this launch (bench.py's roofline_useful)
+    const unsigned long long ev = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)diag_evals);
+    const unsigned long long qu = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)diag_queries);
+    const unsigned long long in = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)diag_inliers);
+    if ((tid & 31) == 0 && a.diag) { atomicAdd(a.diag + 0, ev); atomicAdd(a.diag + 1, qu); atomicAdd(a.diag + 2, in); }
+  }
 }
 
 __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_kernel(const IcpArgs a) {
@@ -511,6 +591,15 @@ __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_ker
 // Large scans (config C4): same algorithm, working set in the CTA's global workspace (L2/L1 resident).
 __global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_kernel(const IcpArgs a) {
   icp_pair_body<kThreadsL2, true, false>(a);
+}
+
+// Diagnostics instantiation (ccicp_params.flags & CCICP_F_DIAG_COUNTS): same algorithm, counts distance evaluations,
+// searched queries and accepted pairs of the launch; never the timed kernel.
+__global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_diag_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsOnChip, false, false, false, true>(a);
+}
+__global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_diag_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsL2, true, false, false, true>(a);
 }
 
 // CCICP_F_EXACT_SUMS instantiations (separate kernels so the default ones carry none of their register pressure).
@@ -526,6 +615,14 @@ __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_tri
 }
 __global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_trim_kernel(const IcpArgs a) {
   icp_pair_body<kThreadsL2, true, false, true>(a);
+}
+
+// Problems of this launch whose default-mode solve met a (nearly) rank-deficient H: listed for the exact-order re-run.
+__global__ void collect_retry_kernel(const ccicp_result* __restrict__ res, int first_prob, int n_prob, int32_t* __restrict__ list,
+                                     int32_t* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_prob) return;
+  if (res[first_prob + i].status & CCICP_ST_DEGENERATE) list[atomicAdd(count, 1)] = first_prob + i;
 }
 
 // best-of-seeds: one warp per pair.  Default: arg-min of score over seeds with num_corr >= min_corr_frac * n_scene,

@@ -45,6 +45,59 @@ def gather_records(local, world, n_total=None):
     return torch.cat(parts)
 
 
+class RecordGather:
+    """The per-step gather of bench.py, taken off the critical path: after the kernel of step k has been enqueued on the
+    compute stream, step() snapshots the rank's records into one of two staging buffers (so the kernel of step k+1 may
+    overwrite them) and all-gathers that snapshot on a side stream, i.e. under the kernel of step k+1.  drain() makes
+    the compute stream wait for every gather issued so far (call it before the closing event of a timed region: the
+    gathers belong to the region).  On CPU tensors (gloo tests) the same calls run synchronously."""
+
+    def __init__(self, local, world, n_total, compute_stream=None):
+        import torch
+        self.local, self.world, self.n_total, self.cs = local, world, n_total, compute_stream
+        self.cuda = local.is_cuda
+        self.k = 0
+        self.stage = [torch.empty_like(local) for _ in range(2)]
+        self.out = [None, None]
+        if self.cuda:
+            self.side = torch.cuda.Stream(device=local.device)
+            self.copied = [torch.cuda.Event() for _ in range(2)]
+            self.gathered = [None, None]
+
+    def step(self):
+        import torch
+        k = self.k
+        self.k ^= 1
+        if not self.cuda:
+            self.stage[k].copy_(self.local)
+            self.out[k] = gather_records(self.stage[k], self.world, self.n_total)
+            return
+        cs = self.cs or torch.cuda.current_stream()
+        if self.gathered[k] is not None:
+            cs.wait_event(self.gathered[k])            # the gather that last read this staging buffer
+        with torch.cuda.stream(cs):
+            self.stage[k].copy_(self.local, non_blocking=True)
+        self.copied[k].record(cs)
+        self.side.wait_event(self.copied[k])
+        with torch.cuda.stream(self.side):
+            self.out[k] = gather_records(self.stage[k], self.world, self.n_total)
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+        self.gathered[k] = ev
+
+    def drain(self):
+        import torch
+        if self.cuda:
+            (self.cs or torch.cuda.current_stream()).wait_stream(self.side)
+
+    def finish(self):
+        """Waits for everything and returns the records of the last step (all ranks, pair order)."""
+        import torch
+        if self.cuda:
+            self.side.synchronize()
+        return self.out[self.k ^ 1]
+
+
 def records_view(t):
     """uint8 torch tensor (CPU) -> numpy structured array of ccicp_result records."""
     return t.cpu().numpy().view(capi.RESULT_DTYPE)

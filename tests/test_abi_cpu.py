@@ -24,7 +24,7 @@ def test_every_declared_symbol_is_exported():
     assert len(names) >= 12 and set(names) == set(capi.SYMBOLS)
     for n in names:
         assert hasattr(lib, n), n
-    assert lib.ccicp_abi_version() == 3
+    assert lib.ccicp_abi_version() == 4
 
 
 def test_struct_layouts():

@@ -1,5 +1,5 @@
 """The two CPU restatements of CCICP::classifyPoints (oracle/classify_port.py) agree with each other and with
-hand-computed answers (the reference function itself cannot be compiled here: parity unpinned)."""
+hand-computed answers, and both are pinned to the reference's own function compiled from icpTools.cpp:36-103."""
 import numpy as np
 
 from oracle import classify_port as cp
@@ -37,3 +37,22 @@ def test_known_answers():
     # two points in one bin keep input order; bin order is x-major
     e = np.array([[1.1, 5.1, 1], [-2.0, 0.1, 2], [1.2, 5.2, 3], [1.1, -5.0, 4]], np.float32)
     assert cp.classify(e)[2].tolist() == [1, 3, 0, 2]
+
+
+def test_port_is_pinned_to_the_compiled_reference():
+    """oracle/_ref/libclassify_ref.so is CCICP::classifyPoints itself (icpTools.cpp:36-103 compiled unmodified against a
+    pcl::PointCloud shim, oracle/Makefile): the numpy port must reproduce its output order, coordinates and flags."""
+    import pytest
+    from oracle import refbind
+    if not refbind.classify_available():
+        pytest.skip("oracle/_ref/libclassify_ref.so not built (needs /root/reference at build time)")
+    clouds = [synthetic_cloud(s, n) for s, n in ((0, 4000), (1, 70000), (2, 257), (3, 12345))]
+    clouds.append(np.array([[-300, 0, 0], [299.5, 0, 0], [300, 0, 0], [-299.5, 0.2, 0], [1.1, 5.1, 1], [-2.0, 0.1, 2],
+                            [1.2, 5.2, 3], [1.1, -5.0, 4], [1.1, 5.1, 5]], np.float32))
+    clouds.append(np.repeat(np.array([[1.1, 5.1, 1.0]], np.float32), 500, 0))
+    for xyz in clouds:
+        rx, rg = refbind.classify_ref(xyz)
+        px, pg, ps = cp.classify(xyz)
+        assert len(rx) == len(px)
+        assert np.array_equal(rx.view(np.uint32), px.view(np.uint32)) and np.array_equal(rg, pg)
+        assert np.array_equal(xyz[ps].view(np.uint32), rx.view(np.uint32))

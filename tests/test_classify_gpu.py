@@ -1,9 +1,12 @@
-"""GPU classifyPoints (bin + stable radix sort + neighbour occupancy) against the oracle
-restatement: identical point order, flags and source indices (bit-exact: integer / byte work)."""
+"""GPU classifyPoints (bin + stable radix sort + neighbour occupancy) against the REFERENCE's own
+CCICP::classifyPoints (oracle/_ref/libclassify_ref.so: icpTools.cpp:36-103 compiled unmodified, oracle/Makefile) for
+point order, coordinates and flags, and against the numpy port (pinned to the same library in
+tests/test_classify_cpu.py) for the source indices the reference does not carry.  Bit-exact: integer / byte work."""
 import numpy as np
 import pytest
 
 from oracle import classify_port as cp
+from oracle import refbind
 from test_classify_cpu import synthetic_cloud
 
 pytestmark = pytest.mark.gpu
@@ -19,6 +22,10 @@ def _check(ctx, clouds):
         assert len(gx) == len(wx)
         assert np.array_equal(gs, ws), "order differs"
         assert np.array_equal(gx.view(np.uint32), wx.view(np.uint32)) and np.array_equal(gg, wg)
+        if refbind.classify_available() and len(c) and np.isfinite(c[:, :2]).all():     # the reference itself
+            rx, rg = refbind.classify_ref(c)
+            assert len(rx) == len(gx)
+            assert np.array_equal(gx.view(np.uint32), rx.view(np.uint32)) and np.array_equal(gg, rg)
 
 
 def test_single_cloud(ctx):

@@ -41,6 +41,16 @@ def _worker(rank, world, port, n_total, q):
     out = sharding.records_view(sharding.gather_records(local, world, n_total))
     ok = (len(out) == n_total and (out["num_corr"] == np.arange(n_total)).all()
           and (out["t"][:, 0] == np.arange(n_total) * 0.5).all())
+    # bench.py's per-step gather object (double-buffered; synchronous on CPU tensors): three steps, the local records
+    # change between steps like a kernel overwriting them, the result of the LAST step is what finish() returns
+    g = sharding.RecordGather(local, world, n_total)
+    for step in range(3):
+        rec["iters"] = step
+        local.copy_(torch.from_numpy(rec.view(np.uint8).copy()))
+        g.step()
+    g.drain()
+    last = sharding.records_view(g.finish())
+    ok = ok and len(last) == n_total and (last["iters"] == 2).all() and (last["num_corr"] == np.arange(n_total)).all()
     tm = torch.tensor([float(rank + 1)])
     dist.all_reduce(tm, op=dist.ReduceOp.MAX)        # bench.py's max-over-ranks timing reduction
     q.put((rank, bool(ok), float(tm.item())))
@@ -84,3 +94,17 @@ def test_bench_c3_shards_and_chunked_generation():
     assert np.array_equal(off, whole.model_off)
     # C3's initial poses are the truth plus noise, not the identity of C2
     assert np.abs(whole.init - whole.truth).max() > 0 and np.abs(whole.init).max() > 0
+
+
+def test_c_abi_shard_rule_matches_python():
+    """ccicp_shard_range (C ABI, multi-device entry points) splits exactly like sharding.shard_range."""
+    import ctypes as C
+    lib = capi.load()
+    lib.ccicp_shard_range.argtypes = [C.c_int32, C.c_int, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.ccicp_shard_range.restype = None
+    for n in (0, 1, 7, 97, 4096, 262144, 1000003):
+        for world in (1, 2, 3, 4, 8):
+            for r in range(world):
+                b, e = C.c_int32(), C.c_int32()
+                lib.ccicp_shard_range(n, world, r, C.byref(b), C.byref(e))
+                assert (b.value, e.value) == sharding.shard_range(n, r, world)
