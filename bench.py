@@ -356,6 +356,7 @@ def sub_config(torch, dev, ctx, capi, name, workload, batch, init_Rt, n_seeds, p
     barrier = torch.cuda.synchronize
     dev_ms, k_ms, li, e2e_ms, e2e_l = time_legs(torch, ctx, db, stream, steps, warmup, barrier)
     units = db.n_pairs * n_seeds
+    kernel = {0: "icp_pair_kernel", 1: "icp_pair_l2_kernel", 4: "icp_pair_cluster_kernel"}.get(int(li.kernel_variant), kernel)
     dram, _, cap = kernel_traffic(traffic, kernel, db.n_pairs)
     ach = db.alg_bytes / (k_ms * 1e-3) / 1e9
     rec = {"workload": workload, "value": units / (dev_ms * 1e-3), "unit": unit_name, "ms_per_step": dev_ms, "kernel_ms": k_ms,
@@ -478,8 +479,7 @@ def gpu_arm(args, rank, world, local_rank, cpu_lines):
         configs["c4"], n4 = sub_config(
             torch, dev, ctx, capi, "c4", "C4: %d pairs of dense 2-D slices, 32768 beams per scan (%d..%d points per cloud), %d fixed iterations, indist %g"
             % (b4.n_pairs, int((b4.model_off[2::2] - b4.model_off[:-2:2]).min()), b4.max_model, ITERS, INDIST),
-            b4, b4.init_Rt(), 1, prm, args.sub_steps, 2, "icp_pair_cluster_kernel" if ctx_variant_is_cluster(ctx, b4) else "icp_pair_l2_kernel",
-            UNIT, traffic, peak, peak_src, cpu_lines.get("c4"))
+            b4, b4.init_Rt(), 1, prm, args.sub_steps, 2, None, UNIT, traffic, peak, peak_src, cpu_lines.get("c4"))
         del b4
         b5, init5 = c5_inputs(args.c5_pairs, C5_SEEDS, capi.pinned_array)
         prm5 = capi.fixed_iter_params(ITERS, indist=INDIST, flags=capi.F_BEST_OF_SEEDS)
@@ -544,10 +544,6 @@ def gpu_arm(args, rank, world, local_rank, cpu_lines):
         "configs": configs,
     }
     return line
-
-
-def ctx_variant_is_cluster(ctx, batch):
-    return False
 
 
 def main():

@@ -28,7 +28,7 @@ def run(ctx, name, b, prm, n_seeds=1, init=None, reps=3):
     n_prob = b.n_pairs * n_seeds
     print(json.dumps({"config": name, "pairs": b.n_pairs, "seeds": n_seeds, "kernel_ms": k, "host_call_ms": w,
                       "problems_per_s_kernel": n_prob / (k * 1e-3), "problems_per_s_host_call": n_prob / (w * 1e-3),
-                      "variant": "l2" if li.kernel_variant else "on-chip", "grid": li.grid, "block": li.block,
+                      "variant": {0: "on-chip", 1: "l2", 4: "cluster"}.get(int(li.kernel_variant), "?"), "grid": li.grid, "block": li.block,
                       "regs": li.regs_per_thread, "smem": li.smem_bytes, "n_launches": li.n_launches,
                       "mean_num_corr": float(out["num_corr"].mean()), "mean_iters": float(out["iters"].mean()),
                       "tie_replay_pairs": int((out["status"] & capi.ST_TIE_REPLAY != 0).sum())}), flush=True)

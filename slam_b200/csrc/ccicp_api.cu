@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "ccicp_pair_main.cuh"
+#include "ccicp_cluster.cuh"
 #include "pose_math.h"
 #include "classify.cuh"
 #include "lum.cuh"
@@ -34,7 +35,8 @@ struct ccicp_ctx {
   bool chunk_ramp = true;     // CCICP_CHUNK_RAMP=0: equal chunks
   int chunk_pairs = 384;      // CCICP_CHUNK_PAIRS: pairs per H2D/compute chunk of the host-buffer call
   int stage_kb = 200;         // CCICP_STAGE_KB
-  bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the L2 variant
+  bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the large-scan variants
+  bool no_cluster = false;    // diagnostics: CCICP_NO_CLUSTER=1 keeps large scans on the one-CTA-per-pair L2 variant
   void* timed_stream = nullptr;
   DevBuf counter, scratch, all_results, workspace, diag, retry_list;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
@@ -142,8 +144,24 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false) + warm_bytes;
   const bool use_l2 = smem + fa_on.sharedSizeBytes > (size_t)ctx->max_smem_optin || ctx->force_l2;
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
-  int occ = 0;
-  if (use_l2) {
+  // large scans: one thread-block cluster per pair (working sets of ~148 / kCluster pairs stay L2-resident); the
+  // one-CTA-per-pair L2 variant serves the exact-order / trim / diagnostic instantiations and CCICP_NO_CLUSTER=1
+  const bool use_cluster = use_l2 && !exact && !trim && !diag && !ctx->no_cluster;
+  int occ = 0, n_clusters = 0;
+  cudaLaunchConfig_t ccfg{};
+  cudaLaunchAttribute cattr[1];
+  if (use_cluster) {
+    a.stage_cap = (ctx->stage_kb * 1024 / 6) & ~31;
+    smem = (size_t)a.stage_cap * 6;
+    CK(cudaFuncSetAttribute(icp_pair_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cattr[0].id = cudaLaunchAttributeClusterDimension;
+    cattr[0].val.clusterDim.x = kCluster; cattr[0].val.clusterDim.y = 1; cattr[0].val.clusterDim.z = 1;
+    ccfg.gridDim = dim3((unsigned)(kCluster * ctx->sm_count), 1, 1); ccfg.blockDim = dim3(kThreadsCl, 1, 1);
+    ccfg.dynamicSmemBytes = smem; ccfg.stream = st; ccfg.attrs = cattr; ccfg.numAttrs = 1;
+    CK(cudaOccupancyMaxActiveClusters(&n_clusters, icp_pair_cluster_kernel, &ccfg));
+    if (n_clusters < 1) return CCICP_E_TOO_LARGE;
+    occ = 1;
+  } else if (use_l2) {
     // dynamic shared memory of the L2 variant = staging arrays of the cooperative tie replay (float + u16 per element);
     // what is left of the SM's 256 KB stays L1 cache for the workspace
     a.stage_cap = (ctx->stage_kb * 1024 / 6) & ~31;
@@ -155,7 +173,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_on, threads, smem));
   }
   if (occ < 1) return CCICP_E_TOO_LARGE;
-  const int resident = occ * ctx->sm_count;
+  const int resident = use_cluster ? n_clusters * kCluster : occ * ctx->sm_count;
 
   const bool best_of = (prm->flags & CCICP_F_BEST_OF_SEEDS) && n_seeds > 1;
   int items_per_pair = 1, seeds_per_item = n_seeds;
@@ -170,7 +188,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     items_per_pair = (n_seeds + seeds_per_item - 1) / seeds_per_item;
   }
   const long long n_items = (long long)n_pairs * items_per_pair;
-  const int grid = (int)(n_items < resident ? n_items : resident);
+  int grid = (int)(n_items < resident ? n_items : resident);
+  if (use_cluster) grid = kCluster * (int)(n_items < n_clusters ? n_items : n_clusters);
 
   ccicp_result* kernel_out = d_out;
   if (best_of) {
@@ -190,8 +209,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   }
 
   if (use_l2) {
-    a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true) + warm_bytes;
-    const size_t ws_slot = a.workspace_per_cta * (size_t)resident;
+    a.workspace_per_cta = workset_bytes(a.mcap, a.scap, a.ccap, true) + warm_bytes + (use_cluster ? 128 : 0);   // per cluster there
+    const size_t ws_slot = a.workspace_per_cta * (size_t)(use_cluster ? n_clusters : resident);
     if (ctx->workspace.cap < ws_slot * n_slots) {
       if (slot != 0) return CCICP_E_INVALID;
       rc = reserve(ctx, ctx->workspace, ws_slot * n_slots);
@@ -219,7 +238,10 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
 
   CK(cudaMemsetAsync(cnt, 0, 16, st));
   if (slot == 0) CK(cudaEventRecord(ctx->ev[2], st));
-  if (use_l2) k_l2<<<grid, threads, smem, st>>>(a);
+  if (use_cluster) {
+    ccfg.gridDim = dim3((unsigned)grid, 1, 1);
+    CK(cudaLaunchKernelEx(&ccfg, icp_pair_cluster_kernel, a));
+  } else if (use_l2) k_l2<<<grid, threads, smem, st>>>(a);
   else k_on<<<grid, threads, smem, st>>>(a);
   CK(cudaGetLastError());
   ctx->info.n_launches += 1;
@@ -247,7 +269,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     }
     if (occ2 < 1) return CCICP_E_TOO_LARGE;
     if (occ2 > occ) occ2 = occ;                   // the scratch and the L2 workspace are sized for `resident` CTAs
-    const long long res2 = (long long)occ2 * ctx->sm_count;
+    long long res2 = (long long)occ2 * ctx->sm_count;
+    if (use_cluster && res2 > n_clusters) res2 = n_clusters;     // the workspace holds one working set per CLUSTER of the main launch
     const int grid2 = (int)((long long)n_prob < res2 ? (long long)n_prob : res2);
     if (use_l2) k2_l2<<<grid2, threads, smem, st>>>(a2);
     else k2_on<<<grid2, threads, smem, st>>>(a2);
@@ -267,7 +290,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   cudaFuncAttributes fa = fa_on;
   if (use_l2) CK(cudaFuncGetAttributes(&fa, k_l2));
   ctx->info.grid = grid; ctx->info.block = threads; ctx->info.smem_bytes = (int)(smem + fa.sharedSizeBytes);
-  ctx->info.regs_per_thread = fa.numRegs; ctx->info.blocks_per_sm = occ; ctx->info.kernel_variant = use_l2 ? 1 : 0;
+  if (use_cluster) CK(cudaFuncGetAttributes(&fa, icp_pair_cluster_kernel));
+  ctx->info.regs_per_thread = fa.numRegs; ctx->info.blocks_per_sm = occ; ctx->info.kernel_variant = use_cluster ? 4 : use_l2 ? 1 : 0;
   ctx->info.sm_count = ctx->sm_count;
   return CCICP_OK;
 }
@@ -324,6 +348,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   if (!ctx) return CCICP_E_NOMEM;
   ctx->device = device;
   { const char* e = getenv("CCICP_FORCE_L2"); ctx->force_l2 = e && e[0] == '1'; }
+  { const char* e = getenv("CCICP_NO_CLUSTER"); ctx->no_cluster = e && e[0] == '1'; }
   { const char* e = getenv("CCICP_CHUNK_PAIRS"); if (e && atoi(e) >= 16) ctx->chunk_pairs = atoi(e); }
   { const char* e = getenv("CCICP_CHUNK_RAMP"); if (e) ctx->chunk_ramp = atoi(e) != 0; }
   { const char* e = getenv("CCICP_STAGE_KB"); if (e && atoi(e) >= 1 && atoi(e) <= 216) ctx->stage_kb = atoi(e); }

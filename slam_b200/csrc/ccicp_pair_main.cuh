@@ -3,6 +3,9 @@
 // iterations of every seed in the chunk, entirely in shared memory/registers.
 #pragma once
 #include "ccicp_pair_kernel.cuh"
+#ifndef CCICP_SOLVE_ALL
+#define CCICP_SOLVE_ALL 0
+#endif
 #include "exact_solve.cuh"
 
 namespace ccicp {
@@ -418,6 +421,33 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             publish_partials(s.red, v, cnt, tid);
             __syncthreads();
           }
+#if CCICP_SOLVE_ALL
+          // (experiment) every warp adds the partials and solves redundantly: no second barrier, 8x the FP64 tail
+          int n;
+          {
+            n = gather_partials<kWarps>(s.red, v, tid & 31);
+            if (n > 0) {
+              const double dm0 = v[0] / (double)n, dm1 = v[1] / (double)n, dt0 = v[2] / (double)n, dt1 = v[3] / (double)n;
+              const double mu_m[2] = {pcx + dm0, pcy + dm1};
+              const double mu_t[2] = {pcx + dt0, pcy + dt1};
+              const double H[4] = {v[4] - v[2] * dm0, v[5] - v[2] * dm1, v[6] - v[3] * dm0, v[7] - v[3] * dm1};
+              if (tid == 0) {
+#pragma unroll
+                for (int q = 0; q < 6; q++) s.rtprev[q] = Rt[q];
+              }
+              last_delta = solve_and_compose(H, mu_m, mu_t, Rt, status);
+            }
+          }
+          iters++;
+          if (n == 0) {
+            last_delta = -1.0; last_failed = true;
+            if (!(-1.0 < a.min_delta)) iters = a.max_iter;
+            break;
+          }
+          last_failed = false; have_ok = true; num_corr = n;
+          if (kDiag) diag_inliers += (tid == 0) ? n : 0;
+          if (last_delta < a.min_delta) { status |= CCICP_ST_CONVERGED; break; }
+#else
           // ---- a7..a9 on ONE warp: totals, centroids, centred cross-covariance, solve, compose
           if (tid < 32) {
             const int n = gather_partials<kWarps>(s.red, v, tid);
@@ -468,6 +498,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
           status |= ((const uint32_t*)&sol_s[7])[1];
           if (kDiag) diag_inliers += (tid == 0) ? n : 0;
           if (last_delta < a.min_delta) { status |= CCICP_ST_CONVERGED; break; }
+#endif
         }
         if (!have_ok && iters > 0) status |= CCICP_ST_NO_CORR;   // max_iter <= 0: no fitStep ran, the reference reports nothing
       }
