@@ -191,6 +191,19 @@ int ccicp_register_batch_device_ex(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_se
                                    const double* d_init_Rt, const ccicp_params* params,
                                    ccicp_result* d_out, int32_t* d_corr_idx,
                                    int32_t max_model, int32_t max_scene, int32_t max_cells_hint, void* stream);
+/* ---- scan table: key-frame scans uploaded once, pairs as index lists ---------------------------------------------
+ * Loop-closure batches reuse every key-frame scan many times: graph_slam registers each new key frame against its K = 3
+ * nearest key frames plus the previous one (graph_slam/include/graph_slam/graphSlamTools.h:26-36,
+ * graphSlamTools.cpp:72-106, 406-425), so a batch of P candidate pairs touches far fewer than 2 P distinct scans.
+ * ccicp_scans_upload copies the scans to the device once (scan_off[2*n_scans+1]: GA block then NGA block per scan, as
+ * model_off above; replaces the ctx's previous table); ccicp_register_scan_pairs then registers scan scene_scan[p]
+ * (the "template") against scan model_scan[p] for every pair with the same contract as ccicp_register_batch, uploading
+ * only the two index lists and the initial transforms.  No correspondence indices on this path.  Synchronous.      */
+int ccicp_scans_upload(ccicp_ctx* ctx, int32_t n_scans, const double* scan_xy, const int32_t* scan_off);
+int ccicp_register_scan_pairs(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
+                              const int32_t* model_scan, const int32_t* scene_scan,
+                              const double* init_Rt, const ccicp_params* params, ccicp_result* out);
+
 int32_t ccicp_grid_cells(int32_t n_class_points);   /* cells of the table for a class of n model points */
 int ccicp_stream_sync(ccicp_ctx* ctx, void* stream);
 

@@ -89,7 +89,7 @@ def build_scangen(force=False, verbose=False):
 def build_host_tests(force=False, verbose=False):
     d = os.path.join(ROOT, "tests", "host")
     out = os.path.join(d, "libkdreplay_host.so")
-    srcs = [os.path.join(d, "kdreplay_host.cpp"), os.path.join(CSRC, "kdreplay.h")]
+    srcs = [os.path.join(d, "kdreplay_host.cpp"), os.path.join(d, "kdreplay_ref.h"), os.path.join(CSRC, "kdreplay.h")]
     if force or _newer(out, srcs):
         _run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", out, srcs[0]], verbose)
     # host build of the grid search (nn_grid.h) for the CPU exactness test
@@ -116,6 +116,11 @@ def build_callsite(force=False, verbose=False):
     if force or _newer(out2, [src2, hdr2, os.path.join(ROOT, "include", "ccicp2d_b200.h"), os.path.join(LIB, "libccicp2d_b200.so")]):
         _run(["g++", "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(ROOT, "include"), "-o", out2, src2, "-L" + LIB,
               "-lccicp2d_b200", "-Wl,-rpath,$ORIGIN/../../slam_b200/lib"], verbose)
+    # several host threads on the reference's class surface (SURVEY.md 8(b) threading)
+    out4, src4 = os.path.join(d, "facade_threads_b200"), os.path.join(d, "facade_threads.cpp")
+    if os.path.exists(src4) and (force or _newer(out4, [src4, os.path.join(LIB, "libccicp2d.so"), os.path.join(LIB, "libscangen.so")])):
+        _run(["g++", "-O2", "-std=c++17", "-pthread", "-I" + os.path.join(ROOT, "include"), "-o", out4, src4, "-L" + LIB,
+              "-lccicp2d", "-lccicp2d_b200", "-lscangen", "-Wl,-rpath,$ORIGIN/../../slam_b200/lib"], verbose)
     # a C++ host driving several GPUs through the multi-device entry points (no Python, no torch)
     out3, src3 = os.path.join(d, "multi_demo_b200"), os.path.join(d, "multi_demo.cu")
     if os.path.exists(src3) and (force or _newer(out3, [src3, os.path.join(ROOT, "include", "ccicp2d_b200.h"),

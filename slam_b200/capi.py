@@ -47,7 +47,7 @@ SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror
            "ccicp_grid_cells", "ccicp_edge_information_lum", "ccicp_knn_candidates", "ccicp_get_diag_counts",
            "ccicp_multi_create", "ccicp_multi_destroy", "ccicp_multi_device_count", "ccicp_multi_ctx", "ccicp_multi_last_error",
            "ccicp_shard_range", "ccicp_register_batch_multi", "ccicp_register_batch_multi_device", "ccicp_multi_sync",
-           "ccicp_multi_gather_kind"]
+           "ccicp_multi_gather_kind", "ccicp_scans_upload", "ccicp_register_scan_pairs"]
 
 _lib = None
 
@@ -89,6 +89,8 @@ def load():
     lib.ccicp_host_free.argtypes = [vp]
     lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
     lib.ccicp_get_diag_counts.argtypes = [vp, vp]
+    lib.ccicp_scans_upload.argtypes = [vp, i32, vp, vp]
+    lib.ccicp_register_scan_pairs.argtypes = [vp, i32, i32, vp, vp, vp, C.POINTER(Params), vp]
     lib.ccicp_match_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
     lib.ccicp_classify_points.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     lib.ccicp_classify_points_device.argtypes = [vp, i32, vp, vp, C.c_int64, vp, vp, vp, vp, vp]
@@ -225,6 +227,26 @@ class Context:
 
     def sync(self, stream=None):
         self._check(self.lib.ccicp_stream_sync(self.h, stream or None))
+
+    def scans_upload(self, scan_xy, scan_off):
+        """ccicp_scans_upload: the ctx's scan table (float64 xy, int32 offsets [2*n_scans+1])."""
+        scan_off = np.ascontiguousarray(scan_off, np.int32)
+        scan_xy = np.ascontiguousarray(scan_xy, np.float64)
+        self._check(self.lib.ccicp_scans_upload(self.h, (len(scan_off) - 1) // 2, _ptr(scan_xy), _ptr(scan_off)))
+
+    def register_scan_pairs(self, model_scan, scene_scan, init_Rt, params, n_seeds=1, out=None):
+        """ccicp_register_scan_pairs: pair p registers scan scene_scan[p] against scan model_scan[p] of the table."""
+        model_scan = np.ascontiguousarray(model_scan, np.int32)
+        scene_scan = np.ascontiguousarray(scene_scan, np.int32)
+        n_pairs = len(model_scan)
+        init_Rt = np.ascontiguousarray(init_Rt, np.float64)
+        assert init_Rt.size == n_pairs * n_seeds * 6 and len(scene_scan) == n_pairs
+        best_of = bool(params.flags & F_BEST_OF_SEEDS) and n_seeds > 1
+        if out is None:
+            out = np.zeros(n_pairs if best_of else n_pairs * n_seeds, RESULT_DTYPE)
+        self._check(self.lib.ccicp_register_scan_pairs(self.h, n_pairs, n_seeds, _ptr(model_scan), _ptr(scene_scan), _ptr(init_Rt),
+                                                       C.byref(params), _ptr(out)))
+        return out
 
     def diag_counts(self):
         """(distance evaluations, queries searched, accepted pairs) of the F_DIAG_COUNTS launches since the last call."""

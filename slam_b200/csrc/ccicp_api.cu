@@ -36,10 +36,13 @@ struct ccicp_ctx {
   int chunk_pairs = 384;      // CCICP_CHUNK_PAIRS: pairs per H2D/compute chunk of the host-buffer call
   int stage_kb = 200;         // CCICP_STAGE_KB
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the large-scan variants
-  bool no_cluster = false;    // diagnostics: CCICP_NO_CLUSTER=1 keeps large scans on the one-CTA-per-pair L2 variant
+  bool cluster = false;       // CCICP_CLUSTER=1: large scans run one thread-block cluster per pair (measured slower than the L2 variant on C4)
   void* timed_stream = nullptr;
   DevBuf counter, scratch, all_results, workspace, diag, retry_list;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
+  DevBuf t_xy, t_off, t_mid, t_sid;        // scan table (ccicp_scans_upload) and the id lists of the last scan-pair call
+  int32_t t_scans = 0, t_max_pts = 0, t_max_cells = 0;
+  std::vector<int32_t> t_size;             // points per scan (host copy, argument checks)
   DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap, c_tile_base, c_tile_seg, c_group_base;            // classification scratch
   DevBuf l_src, l_soff, l_tgt, l_toff, l_dist, l_idx, l_info, l_num, l_status;   // Lu-Milios edge information
   DevBuf c_xyz, c_off, c_out_xyz, c_out_ga, c_out_src, c_out_cnt;             // classification, host-buffer path
@@ -110,7 +113,8 @@ int max_cells_for(int max_model) {
 int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs, int32_t n_seeds, const double* d_model_xy, const int32_t* d_model_off,
                const double* d_scene_xy, const int32_t* d_scene_off, const double* d_init_Rt,
                const ccicp_params* prm, ccicp_result* d_out, int32_t* d_corr, int32_t max_model, int32_t max_scene,
-               int32_t max_cells, int64_t total_scene, cudaStream_t st, int n_slots = 1) {
+               int32_t max_cells, int64_t total_scene, cudaStream_t st, int n_slots = 1,
+               const int32_t* d_model_id = nullptr, const int32_t* d_scene_id = nullptr) {
   // n_slots = launches of this call that may be in flight together (chunked host path: up to 4); each gets its own
   // tie-replay scratch and L2 workspace, sized by the first launch of the call
   if (slot == 0) ctx->info.n_launches = 0;
@@ -144,9 +148,10 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false) + warm_bytes;
   const bool use_l2 = smem + fa_on.sharedSizeBytes > (size_t)ctx->max_smem_optin || ctx->force_l2;
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
-  // large scans: one thread-block cluster per pair (working sets of ~148 / kCluster pairs stay L2-resident); the
-  // one-CTA-per-pair L2 variant serves the exact-order / trim / diagnostic instantiations and CCICP_NO_CLUSTER=1
-  const bool use_cluster = use_l2 && !exact && !trim && !diag && !ctx->no_cluster;
+  // large scans: the one-CTA-per-pair L2 variant by default; with CCICP_CLUSTER=1 one thread-block cluster per pair
+  // (working sets of ~148 / kCluster pairs stay L2-resident: 0.23 GB instead of 4.6 GB of DRAM reads per wave, but the
+  // cluster barriers cost more than the DRAM latency they remove: 7.1 k against 10.5 k pairs/s on C4)
+  const bool use_cluster = use_l2 && !exact && !trim && !diag && ctx->cluster;
   int occ = 0, n_clusters = 0;
   cudaLaunchConfig_t ccfg{};
   cudaLaunchAttribute cattr[1];
@@ -220,6 +225,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   }
   a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
   a.init_Rt = d_init_Rt; a.out = kernel_out; a.corr_idx = d_corr;
+  a.model_id = d_model_id; a.scene_id = d_scene_id;
   int32_t* cnt = (int32_t*)ctx->counter.p + 4 * (slot & 15);      // {work, retry work, retry count, -} of this slot
   a.work_counter = cnt;
   a.scratch = (char*)ctx->scratch.p + (size_t)(slot % n_slots) * per_slot; a.scratch_per_cta = per_cta;
@@ -280,7 +286,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   if (best_of) {
     const int threads = 128, warps_per_block = threads / 32;
     select_best_seed_kernel<<<(n_pairs + warps_per_block - 1) / warps_per_block, threads, 0, st>>>(
-        kernel_out, d_out, d_scene_off + 2 * (size_t)pair_base, n_pairs, n_seeds, prm->min_corr_frac,
+        kernel_out, d_out, d_scene_off + (d_scene_id ? 0 : 2 * (size_t)pair_base), d_scene_id ? d_scene_id + pair_base : nullptr, n_pairs,
+        n_seeds, prm->min_corr_frac,
         (prm->flags & CCICP_F_FIRST_BELOW) ? prm->score_threshold : -1.0);
     CK(cudaGetLastError());
     ctx->info.n_launches += 1;
@@ -348,7 +355,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   if (!ctx) return CCICP_E_NOMEM;
   ctx->device = device;
   { const char* e = getenv("CCICP_FORCE_L2"); ctx->force_l2 = e && e[0] == '1'; }
-  { const char* e = getenv("CCICP_NO_CLUSTER"); ctx->no_cluster = e && e[0] == '1'; }
+  { const char* e = getenv("CCICP_CLUSTER"); ctx->cluster = e && e[0] == '1'; }
   { const char* e = getenv("CCICP_CHUNK_PAIRS"); if (e && atoi(e) >= 16) ctx->chunk_pairs = atoi(e); }
   { const char* e = getenv("CCICP_CHUNK_RAMP"); if (e) ctx->chunk_ramp = atoi(e) != 0; }
   { const char* e = getenv("CCICP_STAGE_KB"); if (e && atoi(e) >= 1 && atoi(e) <= 216) ctx->stage_kb = atoi(e); }
@@ -374,7 +381,7 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   if (!ctx) return CCICP_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->retry_list, &ctx->diag, &ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
+  DevBuf* bufs[] = {&ctx->t_xy, &ctx->t_off, &ctx->t_mid, &ctx->t_sid, &ctx->retry_list, &ctx->diag, &ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
                     &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_tile_base, &ctx->c_tile_seg, &ctx->c_group_base, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
                     &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
@@ -538,6 +545,69 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   if (n_chunks == 1) CK(cudaStreamSynchronize(st));
   else { for (auto& ks : ctx->kstream) CK(cudaStreamSynchronize(ks)); }
   if (out_dst != out) memcpy(out, out_dst, n_out * sizeof(ccicp_result));
+  ctx->timed_copies = true;
+  return CCICP_OK;
+}
+
+// ---- scan table: key-frame scans uploaded once, pairs as (model scan, scene scan) index lists ----------------------
+int ccicp_scans_upload(ccicp_ctx* ctx, int32_t n_scans, const double* scan_xy, const int32_t* scan_off) {
+  if (!ctx || n_scans < 0) return CCICP_E_INVALID;
+  ctx->t_scans = 0; ctx->t_max_pts = 0; ctx->t_max_cells = 0; ctx->t_size.clear();
+  if (n_scans == 0) return CCICP_OK;
+  if (!scan_off || scan_off[0] != 0 || !offsets_ok(scan_off, n_scans)) return CCICP_E_INVALID;
+  const int64_t n_pts = scan_off[2 * (size_t)n_scans];
+  if (n_pts > 0 && !scan_xy) return CCICP_E_INVALID;
+  try { ctx->t_size.resize((size_t)n_scans); } catch (const std::bad_alloc&) { return CCICP_E_NOMEM; }
+  int max_pts = 0, max_cells = 0;
+  for (int32_t k = 0; k < n_scans; k++) {
+    const int a = scan_off[2 * k + 1] - scan_off[2 * k], b = scan_off[2 * k + 2] - scan_off[2 * k + 1];
+    ctx->t_size[k] = a + b;
+    if (a + b > max_pts) max_pts = a + b;
+    const int ga = grid_side(a), gb = grid_side(b);
+    if (ga * ga + gb * gb > max_cells) max_cells = ga * ga + gb * gb;
+  }
+  if (max_pts > CCICP_MAX_POINTS - 1) return CCICP_E_TOO_LARGE;
+  CK(cudaSetDevice(ctx->device));
+  int rc;
+  const size_t off_bytes = (2 * (size_t)n_scans + 1) * 4;
+  if ((rc = reserve(ctx, ctx->t_xy, (size_t)n_pts * 16 + 16))) return rc;
+  if ((rc = reserve(ctx, ctx->t_off, off_bytes))) return rc;
+  if (n_pts) CK(cudaMemcpyAsync(ctx->t_xy.p, scan_xy, (size_t)n_pts * 16, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->t_off.p, scan_off, off_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  ctx->t_scans = n_scans; ctx->t_max_pts = max_pts; ctx->t_max_cells = max_cells;
+  return CCICP_OK;
+}
+
+int ccicp_register_scan_pairs(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const int32_t* model_scan,
+                              const int32_t* scene_scan, const double* init_Rt, const ccicp_params* params, ccicp_result* out) {
+  if (!ctx || !params || n_pairs < 0 || n_seeds < 1) return CCICP_E_INVALID;
+  if (n_pairs == 0) return CCICP_OK;
+  if (!model_scan || !scene_scan || !init_Rt || !out || ctx->t_scans <= 0) return CCICP_E_INVALID;
+  for (int32_t p = 0; p < n_pairs; p++)
+    if (model_scan[p] < 0 || model_scan[p] >= ctx->t_scans || scene_scan[p] < 0 || scene_scan[p] >= ctx->t_scans) return CCICP_E_INVALID;
+  const bool best_of = (params->flags & CCICP_F_BEST_OF_SEEDS) && n_seeds > 1;
+  const size_t n_prob = (size_t)n_pairs * n_seeds, n_out = best_of ? (size_t)n_pairs : n_prob;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  if ((rc = reserve(ctx, ctx->t_mid, (size_t)n_pairs * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->t_sid, (size_t)n_pairs * 4))) return rc;
+  if ((rc = reserve(ctx, ctx->d_init, n_prob * 48))) return rc;
+  if ((rc = reserve(ctx, ctx->d_out, n_out * sizeof(ccicp_result)))) return rc;
+  CK(cudaEventRecord(ctx->ev[0], st));
+  CK(cudaMemcpyAsync(ctx->t_mid.p, model_scan, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->t_sid.p, scene_scan, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->d_init.p, init_Rt, n_prob * 48, cudaMemcpyHostToDevice, st));
+  CK(cudaEventRecord(ctx->ev[1], st));
+  rc = launch_icp(ctx, 0, 0, n_pairs, n_seeds, (const double*)ctx->t_xy.p, (const int32_t*)ctx->t_off.p, (const double*)ctx->t_xy.p,
+                  (const int32_t*)ctx->t_off.p, (const double*)ctx->d_init.p, params, (ccicp_result*)ctx->d_out.p, nullptr,
+                  ctx->t_max_pts, ctx->t_max_pts, ctx->t_max_cells, 0, st, 1, (const int32_t*)ctx->t_mid.p, (const int32_t*)ctx->t_sid.p);
+  if (rc) { cudaDeviceSynchronize(); return rc; }
+  CK(cudaEventRecord(ctx->ev[4], st));
+  CK(cudaMemcpyAsync(out, ctx->d_out.p, n_out * sizeof(ccicp_result), cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(ctx->ev[5], st));
+  CK(cudaStreamSynchronize(st));
   ctx->timed_copies = true;
   return CCICP_OK;
 }

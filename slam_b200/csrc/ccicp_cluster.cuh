@@ -265,8 +265,9 @@ __global__ void __launch_bounds__(kThreadsCl, 1) icp_pair_cluster_kernel(const I
     const int pair = a.pair_base + item / a.items_per_pair;
     const int seed0 = (item % a.items_per_pair) * a.seeds_per_item;
     const int seed1 = min(seed0 + a.seeds_per_item, a.n_seeds);
-    const int m0 = a.model_off[2 * pair], nmGA = a.model_off[2 * pair + 1] - m0, nmNGA = a.model_off[2 * pair + 2] - a.model_off[2 * pair + 1];
-    const int s0 = a.scene_off[2 * pair], nsGA = a.scene_off[2 * pair + 1] - s0, nsNGA = a.scene_off[2 * pair + 2] - a.scene_off[2 * pair + 1];
+    const int mi = a.model_id ? a.model_id[pair] : pair, si = a.scene_id ? a.scene_id[pair] : pair;
+    const int m0 = a.model_off[2 * mi], nmGA = a.model_off[2 * mi + 1] - m0, nmNGA = a.model_off[2 * mi + 2] - a.model_off[2 * mi + 1];
+    const int s0 = a.scene_off[2 * si], nsGA = a.scene_off[2 * si + 1] - s0, nsNGA = a.scene_off[2 * si + 2] - a.scene_off[2 * si + 1];
     const int ns = nsGA + nsNGA;
     const bool model_ok = nmGA + nmNGA >= 5, scene_ok = ns >= 5;
     const bool fits = grid_side(nmGA) * grid_side(nmGA) + grid_side(nmNGA) * grid_side(nmNGA) <= a.ccap &&

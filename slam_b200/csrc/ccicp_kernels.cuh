@@ -55,6 +55,8 @@ struct IcpArgs {
   int64_t total_scene;           // corr_idx seed stride (scene points in the whole batch)
   int32_t mcap, scap, ccap;      // shared-memory capacities: model points, scene points, cells
   int32_t max_model;             // scratch sizing
+  const int32_t* model_id; const int32_t* scene_id;      // scan-table form: pair p registers scan scene_id[p] against scan model_id[p]
+                                                         // (both index the same offsets / xy arrays); NULL = pair p's own blocks
   const int32_t* item_list; const int32_t* item_count;   // exact-order re-run: listed problem ids (pair * n_seeds + seed) and their count
   unsigned long long* diag;      // diagnostics instantiation: {distance evaluations, searched queries, accepted pairs}
 };

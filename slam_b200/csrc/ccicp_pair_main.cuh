@@ -209,23 +209,10 @@ __device__ __noinline__ void exact_step(const Smem& s, const double* Rt, int ns,
 // matrix); its match only serves as the starting bound of the next iteration's search.  The distances are computed once
 // per call with the search's own float expression and kept as the select's keys.
 template <int kThreads>
-__device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double* Rt, int ns, int tid, uint32_t* th,
-                                         uint32_t* keys) {
-  // keys[i] = bit pattern of the gated squared distance of scene point i, computed once (0xFFFFFFFF = not gated: never
-  // matches a prefix because a finite float's top byte is < 0xFF); every thread reads back only what it wrote
-  for (int i = tid; i < ns; i += kThreads) {
-    const unsigned slot = s.slots[i];
-    uint32_t key = 0xFFFFFFFFu;
-    if (slot != kNoSlot) {
-      const double2 sp = s.scene[i];
-      float qx, qy;
-      transform(Rt, sp.x, sp.y, qx, qy);
-      const float2 p = s.mpts[slot];
-      const float dx = __fsub_rn(p.x, qx), dy = __fsub_rn(p.y, qy);
-      key = __float_as_uint(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-    }
-    keys[i] = key;
-  }
+__device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, int ns, int tid, uint32_t* th, uint32_t* keys) {
+  // keys[i] = bit pattern of the gated squared distance of scene point i, left there by the search loop that found it
+  // (0xFFFFFFFF = not gated: never matches a prefix because a finite float's top byte is < 0xFF); every thread reads
+  // back only what it wrote
   uint32_t prefix = 0, mask = 0;
   for (int pass = 3; pass >= 0; pass--) {
     __syncthreads();
@@ -259,10 +246,13 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, const double
         th[256] = (uint32_t)(tid * 8 + dgt);
         th[257] = k - run;                                 // rank inside the chosen digit
       }
-      if (tid == 0) th[258] = total;
+      if (tid == 0) { th[258] = total; if (pass == 3) th[259] = (k >= total) ? 1u : 0u; }
     }
     __syncthreads();
-    if (th[258] == 0) return;                              // nothing gated: nothing to trim (uniform; all keys are 'none')
+    if (th[258] == 0 || th[259]) {                         // nothing gated, or every gated pair is kept (trim_frac = 1):
+      for (int i = tid; i < ns; i += kThreads) keys[i] = kNoSlot;      // nothing to trim, no further passes (uniform)
+      return;
+    }
     prefix |= th[256] << (8 * pass);
     mask |= 0xFFu << (8 * pass);
   }
@@ -291,7 +281,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   __shared__ GridP grid_s[2];
   __shared__ int misc_s[M_COUNT];
   __shared__ double sol_s[8];          // warp 0 -> CTA: new R,t, delta, {n, status bits} of the iteration
-  __shared__ uint32_t trim_s[kTrim ? 260 : 1];
+  __shared__ uint32_t trim_s[kTrim ? 264 : 1];
   char* base = kGlobal ? a.workspace + (size_t)blockIdx.x * a.workspace_per_cta : smem_raw;
   Smem s = carve<kGlobal>(base, a.mcap, a.scap, a.ccap, red_s, rtprev_s, grid_s, misc_s);
   uint32_t* trim_keys = nullptr;       // kTrim: [scap] behind the carved working set
@@ -324,8 +314,9 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
       seed1 = min(seed0 + a.seeds_per_item, a.n_seeds);
     }
 
-    const int m0 = a.model_off[2 * pair], nmGA = a.model_off[2 * pair + 1] - m0, nmNGA = a.model_off[2 * pair + 2] - a.model_off[2 * pair + 1];
-    const int s0 = a.scene_off[2 * pair], nsGA = a.scene_off[2 * pair + 1] - s0, nsNGA = a.scene_off[2 * pair + 2] - a.scene_off[2 * pair + 1];
+    const int mi = a.model_id ? a.model_id[pair] : pair, si = a.scene_id ? a.scene_id[pair] : pair;
+    const int m0 = a.model_off[2 * mi], nmGA = a.model_off[2 * mi + 1] - m0, nmNGA = a.model_off[2 * mi + 2] - a.model_off[2 * mi + 1];
+    const int s0 = a.scene_off[2 * si], nsGA = a.scene_off[2 * si + 1] - s0, nsNGA = a.scene_off[2 * si + 2] - a.scene_off[2 * si + 1];
     const int ns = nsGA + nsNGA;
     const bool model_ok = nmGA + nmNGA >= 5, scene_ok = ns >= 5;
     // capacity of this launch's working set (a caller-supplied cell hint may be too small for this pair)
@@ -388,10 +379,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
                 slot = (unsigned)bslot;
                 if (tie && replay_on) { pend = 1; atomicOr(&s.tiebits[i >> 5], 1u << (i & 31)); }
               }
-            }
+              if constexpr (kTrim) trim_keys[i] = slot != kNoSlot ? __float_as_uint(best) : 0xFFFFFFFFu;   // the select's key
+            } else if constexpr (kTrim) trim_keys[i] = 0xFFFFFFFFu;
             s.slots[i] = (uint16_t)slot;
           }
-          if constexpr (kTrim) trim_select<kThreads>(a, s, Rt, ns, tid, trim_s, trim_keys);
+          if constexpr (kTrim) trim_select<kThreads>(a, s, ns, tid, trim_s, trim_keys);
           // ---- a7: shifted sums of the accepted pairs; every warp publishes its partials, warp 0 adds them and solves
           double v[8];
           int cnt;
@@ -536,10 +528,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               float best; int bslot, tie;
               nn_search<kGlobal, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
-            }
+              if constexpr (kTrim) trim_keys[i] = slot != kNoSlot ? __float_as_uint(best) : 0xFFFFFFFFu;
+            } else if constexpr (kTrim) trim_keys[i] = 0xFFFFFFFFu;
             s.slots[i] = (uint16_t)slot;
           }
-          if constexpr (kTrim) trim_select<kThreads>(a, s, P, ns, tid, trim_s, trim_keys);
+          if constexpr (kTrim) trim_select<kThreads>(a, s, ns, tid, trim_s, trim_keys);
         }
         const bool want_info = (a.flags & CCICP_F_INFO) != 0;
         const bool fixed_dy = (a.flags & CCICP_F_INFO_FIXED_DY) != 0;
@@ -661,12 +654,13 @@ __global__ void collect_retry_kernel(const ccicp_result* __restrict__ res, int f
 // score / n_scene is below the threshold (global_match.cpp:131-151); if there is none, the arg-min with
 // CCICP_ST_NO_SEED_BELOW.
 __global__ void select_best_seed_kernel(const ccicp_result* __restrict__ all, ccicp_result* __restrict__ out,
-                                        const int32_t* __restrict__ scene_off, int n_pairs, int n_seeds,
-                                        double min_corr_frac, double first_below) {
+                                        const int32_t* __restrict__ scene_off, const int32_t* __restrict__ scene_id,
+                                        int n_pairs, int n_seeds, double min_corr_frac, double first_below) {
   const int pair = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (pair >= n_pairs) return;
-  const double n_scene = (double)(scene_off[2 * pair + 2] - scene_off[2 * pair]);
+  const int sid = scene_id ? scene_id[pair] : pair;
+  const double n_scene = (double)(scene_off[2 * sid + 2] - scene_off[2 * sid]);
   const double need = min_corr_frac * n_scene;
   double best = CUDART_INF;
   int bseed = 0x7fffffff, fseed = 0x7fffffff;

@@ -5,33 +5,39 @@
 // 90-101) and the outputs are left untouched.
 #include <cstdio>
 #include <cstring>
-#include <mutex>
+#include <atomic>
 
 #include "ccicp2d/icpPointToPoint.h"
 #include "ccicp2d_b200.h"
 
 namespace {
-std::mutex g_mu;
-ccicp_ctx* g_ctx = nullptr;
-int g_device = 0;
+// One ccicp_ctx per HOST THREAD (thread_local, destroyed when the thread exits): two threads calling fit() at the same
+// time run on their own streams and buffers.  The reference is not re-entrant at all -- matrix.cpp:26-31 keeps
+// file-static scratch variables, so even distinct Matrix objects race across threads (SURVEY.md 8(b) "Threading").
+std::atomic<int> g_device{0};
+struct ThreadCtx {
+  ccicp_ctx* ctx = nullptr;
+  int device = -1;
+  ~ThreadCtx() { if (ctx) ccicp_destroy(ctx); }
+};
+thread_local ThreadCtx t_ctx;
 
-ccicp_ctx* context() {           // one context per process, created on first use
-  if (!g_ctx) {
-    int rc = ccicp_create(&g_ctx, g_device);
+ccicp_ctx* context() {
+  const int want = g_device.load();
+  if (t_ctx.ctx && t_ctx.device != want) { ccicp_destroy(t_ctx.ctx); t_ctx.ctx = nullptr; }
+  if (!t_ctx.ctx) {
+    int rc = ccicp_create(&t_ctx.ctx, want);
     if (rc != CCICP_OK) {
-      std::fprintf(stderr, "[ccicp2d] ERROR: cannot open CUDA device %d: %s\n", g_device, ccicp_strerror(rc));
-      g_ctx = nullptr;
+      std::fprintf(stderr, "[ccicp2d] ERROR: cannot open CUDA device %d: %s\n", want, ccicp_strerror(rc));
+      t_ctx.ctx = nullptr;
     }
+    t_ctx.device = want;
   }
-  return g_ctx;
+  return t_ctx.ctx;
 }
 }  // namespace
 
-void Icp::setDevice(int device) {
-  std::lock_guard<std::mutex> lk(g_mu);
-  if (g_ctx && device != g_device) { ccicp_destroy(g_ctx); g_ctx = nullptr; }
-  g_device = device;
-}
+void Icp::setDevice(int device) { g_device.store(device); }   // takes effect at each thread's next fit()
 
 Icp::Icp(double* M_GA, double* M_NGA, const int32_t M_GA_num, const int32_t M_NGA_num, const int32_t dim_)
     : M_GA_SIZE(0), M_NGA_SIZE(0), dim(dim_), sub_step(10), max_iter(20), min_delta(1e-6), numCorr(0),
@@ -78,16 +84,13 @@ void Icp::fit(double* T_GA, double* T_NGA, const int32_t T_GA_num, const int32_t
   prm.max_iter = max_iter; prm.min_delta = min_delta; prm.indist = indist; prm.flags = CCICP_F_INFO;
   ccicp_result res;
   std::memset(&res, 0, sizeof(res));
-  int rc;
-  {
-    std::lock_guard<std::mutex> lk(g_mu);
-    ccicp_ctx* ctx = context();
-    if (!ctx) return;
-    rc = ccicp_register_batch(ctx, 1, 1, model_.data(), moff, scene.data(), soff, Rt, &prm, &res, nullptr);
-    if (rc != CCICP_OK)
-      std::fprintf(stderr, "[ccicp2d] ERROR: registration failed: %s %s\n", ccicp_strerror(rc), ccicp_last_cuda_error(ctx));
+  ccicp_ctx* ctx = context();
+  if (!ctx) return;
+  const int rc = ccicp_register_batch(ctx, 1, 1, model_.data(), moff, scene.data(), soff, Rt, &prm, &res, nullptr);
+  if (rc != CCICP_OK) {
+    std::fprintf(stderr, "[ccicp2d] ERROR: registration failed: %s %s\n", ccicp_strerror(rc), ccicp_last_cuda_error(ctx));
+    return;
   }
-  if (rc != CCICP_OK) return;
   last_status = res.status; last_iters = res.iters;
   if (res.status & CCICP_ST_NO_CORR) std::fprintf(stderr, "[ccicp2d] WARN: NO CORRESPONDENCES!!\n");
   R.val[0][0] = res.R[0]; R.val[0][1] = res.R[1]; R.val[1][0] = res.R[2]; R.val[1][1] = res.R[3];

@@ -4,7 +4,7 @@
 #include <cstdint>
 #include <cstring>
 #include <vector>
-#include "../../slam_b200/csrc/kdreplay.h"
+#include "kdreplay_ref.h"
 
 extern "C" {
 

@@ -55,3 +55,13 @@ def test_too_few_points_leave_pose_untouched(tmp_path):
     _write_pair(path, (big[:10], big[10:], big[:2], big[2:4]), (0.25, -0.5, 0.125))     # 4 scene points
     pg, ng, _, err = _run(B200, path, ["5", "-2"])
     assert np.allclose(pg, [0.25, -0.5, 0.125], atol=1e-15) and "Total template has 4 points" in err
+
+
+def test_several_host_threads_share_the_class_surface():
+    """SURVEY.md 8(b) threading: four host threads construct IcpPointToPoint objects and call fit() at the same time
+    (the reference cannot: matrix.cpp:26-31 file-static scratch); every answer equals the single-thread run."""
+    exe = os.path.join(ROOT, "tests", "host", "facade_threads_b200")
+    if not os.path.exists(exe):
+        pytest.fail("tests/host/facade_threads_b200 missing: run __graft_entry__.build()")
+    r = subprocess.run([exe, "4", "6", "5"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0 and "facade_threads OK" in r.stdout, r.stdout

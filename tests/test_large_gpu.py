@@ -1,6 +1,6 @@
 """GPU parity of the large-scan variants of the pair kernel (working set in a global workspace): the cluster-per-pair
-kernel (kernel_variant 4, the default for scans beyond one SM's shared memory) and the one-CTA-per-pair L2 kernel
-(kernel_variant 1: CCICP_NO_CLUSTER=1, and the exact-order / trim instantiations).  Config C4 (32768-point dense
+kernel (kernel_variant 4, opt-in with CCICP_CLUSTER=1) and the one-CTA-per-pair L2 kernel (kernel_variant 1, the default for
+scans beyond one SM's shared memory, and the only one for the exact-order / trim instantiations).  Config C4 (32768-point dense
 slices) and, with CCICP_FORCE_L2=1, the ordinary 1081-beam pairs routed through the same variants."""
 import os
 
@@ -15,27 +15,27 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(params=["cluster", "l2"])
 def l2ctx(request):
-    """Every batch through a large-scan variant: the cluster kernel, or (CCICP_NO_CLUSTER=1) the one-CTA L2 kernel."""
+    """Every batch through a large-scan variant: the one-CTA L2 kernel, or (CCICP_CLUSTER=1) the cluster kernel."""
     os.environ["CCICP_FORCE_L2"] = "1"
-    if request.param == "l2":
-        os.environ["CCICP_NO_CLUSTER"] = "1"
+    if request.param == "cluster":
+        os.environ["CCICP_CLUSTER"] = "1"
     try:
         c = capi.Context(0)
     finally:
         del os.environ["CCICP_FORCE_L2"]
-        os.environ.pop("CCICP_NO_CLUSTER", None)
+        os.environ.pop("CCICP_CLUSTER", None)
     c.want_variant = 4 if request.param == "cluster" else 1
     yield c
     c.close()
 
 
 @pytest.fixture()
-def l2only():
-    os.environ["CCICP_NO_CLUSTER"] = "1"
+def clctx():
+    os.environ["CCICP_CLUSTER"] = "1"
     try:
         c = capi.Context(0)
     finally:
-        del os.environ["CCICP_NO_CLUSTER"]
+        del os.environ["CCICP_CLUSTER"]
     yield c
     c.close()
 
@@ -69,7 +69,7 @@ def test_forced_l2_lockstep_with_ties(l2ctx, oracle):
     assert (res["status"] & capi.ST_TIE_REPLAY).any()
 
 
-def test_l2_tie_replay_on_large_lattice(ctx, l2only, oracle):
+def test_l2_tie_replay_on_large_lattice(ctx, clctx, oracle):
     """16384-point lattice (L2 variant by size): every query is equidistant from four model points, so each one is
     answered by the cooperative kd-tree replay (first iteration) -- the data-parallel partition (kdreplay.h: partition_ranked) splits
     nodes from 14384 points down to the leaves, the 2000-point class exercises ranges shorter than the CTA.  The
@@ -83,7 +83,7 @@ def test_l2_tie_replay_on_large_lattice(ctx, l2only, oracle):
     pair = (model[:nGA], model[nGA:], scene[pick < nGA], scene[pick >= nGA])
     Rt0 = np.array([1.0, 0, 0, 1, 0, 0])
     tr = oracle.trace(*pair, Rt0, max_iter=2, min_delta=-2.0)
-    for c, variant in ((ctx, 4), (l2only, 1)):
+    for c, variant in ((ctx, 1), (clctx, 4)):
         corr, res = gpu_lockstep_corr(c, pair, tr["Rt_trace"][:-1])
         assert c.launch_info().kernel_variant == variant
         assert (corr == tr["corr"]).all()
@@ -91,16 +91,16 @@ def test_l2_tie_replay_on_large_lattice(ctx, l2only, oracle):
         assert int(res["n_tie_replays"][0]) == int(tr["tie"][0].sum()) >= 900      # (float rounding breaks a third of the ties)
 
 
-def test_c4_dense_pair(ctx, l2only, oracle):
-    """Config C4: 32768-beam pairs (do not fit shared memory -> cluster variant; L2 variant with CCICP_NO_CLUSTER=1),
+def test_c4_dense_pair(ctx, clctx, oracle):
+    """Config C4: 32768-beam pairs (do not fit shared memory -> L2 variant; cluster variant with CCICP_CLUSTER=1),
     30 fixed iterations, with the information matrix."""
     b = scangen.generate(5000, 2, config=4)
     assert b.max_model > 30000
     prm = capi.fixed_iter_params(30, flags=capi.F_INFO)
     res, corr = ctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm, want_corr=True)
-    assert ctx.launch_info().kernel_variant == 4
-    res1, corr1 = l2only.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm, want_corr=True)
-    assert l2only.launch_info().kernel_variant == 1
+    assert ctx.launch_info().kernel_variant == 1
+    res1, corr1 = clctx.register_batch(b.model_xy, b.model_off, b.scene_xy, b.scene_off, b.init_Rt(), prm, want_corr=True)
+    assert clctx.launch_info().kernel_variant == 4
     assert (corr == corr1).all() and (res["num_corr"] == res1["num_corr"]).all()
     assert_pose_close(np.c_[res["R"], res["t"]], np.c_[res1["R"], res1["t"]], "cluster vs L2")
     np.testing.assert_allclose(res["info"], res1["info"], rtol=1e-9)
