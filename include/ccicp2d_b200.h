@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CCICP_ABI_VERSION 4
+#define CCICP_ABI_VERSION 5
 
 /* ---- call-level error codes ------------------------------------------- */
 enum {
@@ -84,6 +84,14 @@ enum {
   CCICP_F_TRIM           = 1u << 6, /* north_star extra, NO counterpart in the reference (its only outlier test is the fixed
                                        gate, icpPointToPoint.cpp:76,111): trimmed rejection, keep the params.trim_frac
                                        fraction of the gated correspondences per iteration.  Off in every parity run. */
+  CCICP_F_CURV_GATE      = 1u << 9, /* north_star extra, NO counterpart on the reference's built path (its "cc" is the class
+                                       constraint GA / NGA; its only normal code is the dead icpPointToPlane.cpp:276-348):
+                                       curvature-gated matching.  Every model and scene point gets a curvature from its scan
+                                       neighbours (ccicp_scan_features, params.feat_k / feat_radius); a model point is a
+                                       candidate for a scene point only if the two curvatures differ by at most
+                                       params.curv_tol, IN ADDITION to the class constraint.  Points without a feature are
+                                       compatible with everything; float ties go to the lowest model index (no kd-tree replay:
+                                       there is no reference traversal to follow).  Off in every parity run.              */
   CCICP_F_DIAG_COUNTS    = 1u << 7, /* diagnostics only: run the counting instantiation of the pair kernel (same algorithm and
                                        results, slower) and accumulate the work it did; read with ccicp_get_diag_counts.  Never
                                        set in a timed run.                                                                     */
@@ -110,6 +118,10 @@ typedef struct ccicp_params {
                              (graph_slam/src/graphSlamTools.cpp:332-362, graphSlamTools.h:35-36)    */
   double   trim_frac;     /* CCICP_F_TRIM: fraction in (0, 1] of each iteration's gated correspondences that is kept
                              (those with the smallest squared distance); default 1 = the reference's behaviour     */
+  double   curv_tol;      /* CCICP_F_CURV_GATE: largest |curvature(model) - curvature(scene)| of a candidate (default 0.05) */
+  double   feat_radius;   /* features: neighbours farther than this from the point are ignored [m] (default 0.5)   */
+  int32_t  feat_k;        /* features: index neighbours taken on each side (default 5; icpPointToPlane.cpp used 10 in all) */
+  int32_t  reserved;
 } ccicp_params;
 
 /* One record per (pair, seed) problem -- 160 bytes. */
@@ -203,6 +215,16 @@ int ccicp_scans_upload(ccicp_ctx* ctx, int32_t n_scans, const double* scan_xy, c
 int ccicp_register_scan_pairs(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds,
                               const int32_t* model_scan, const int32_t* scene_scan,
                               const double* init_Rt, const ccicp_params* params, ccicp_result* out);
+
+/* ---- per-point features of a scan: normal and curvature (north_star extra, see CCICP_F_CURV_GATE) ----------------
+ * Shape of the reference's dead computeNormal (ccicp2d/src/icpPointToPlane.cpp:276-338), in 2-D: PCA over the scan
+ * neighbours.  Clouds in the CSR layout of the registration calls (xy FP64, off[2*n_clouds+1]: GA block then NGA block
+ * per cloud).  Neighbours of point i: the points of its own class block within feat_k positions of i (a scan arrives in
+ * beam order) and within feat_radius of it, i included; fewer than 3 -> curvature NaN, normal (0, 0).  With l1 >= l2
+ * the eigenvalues of their scatter matrix: curvature = l2 / (l1 + l2) in [0, 0.5]; normal = unit eigenvector of l2
+ * turned towards the origin of the scan frame.  normal_xy may be NULL.  Host buffers; synchronous.              */
+int ccicp_scan_features(ccicp_ctx* ctx, int32_t n_clouds, const double* xy, const int32_t* off, int32_t feat_k,
+                        double feat_radius, float* normal_xy, float* curvature);
 
 int32_t ccicp_grid_cells(int32_t n_class_points);   /* cells of the table for a class of n model points */
 int ccicp_stream_sync(ccicp_ctx* ctx, void* stream);

@@ -19,13 +19,14 @@ ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1
 ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
 ST_NO_SEED_BELOW, ST_EDGE_REJECTED, ST_EXACT_RETRY = 1024, 2048, 4096
 F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW, F_TRIM = 1, 2, 4, 8, 16, 32, 64
-F_DIAG_COUNTS, F_NO_EXACT_RETRY = 128, 256
+F_DIAG_COUNTS, F_NO_EXACT_RETRY, F_CURV_GATE = 128, 256, 512
 
 
 class Params(C.Structure):
     _fields_ = [("max_iter", C.c_int32), ("flags", C.c_uint32), ("min_delta", C.c_double),
                 ("indist", C.c_double), ("min_corr_frac", C.c_double), ("score_threshold", C.c_double),
-                ("reject_dist", C.c_double), ("reject_rot", C.c_double), ("trim_frac", C.c_double)]
+                ("reject_dist", C.c_double), ("reject_rot", C.c_double), ("trim_frac", C.c_double),
+                ("curv_tol", C.c_double), ("feat_radius", C.c_double), ("feat_k", C.c_int32), ("reserved", C.c_int32)]
 
 
 class LaunchInfo(C.Structure):
@@ -47,7 +48,7 @@ SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror
            "ccicp_grid_cells", "ccicp_edge_information_lum", "ccicp_knn_candidates", "ccicp_get_diag_counts",
            "ccicp_multi_create", "ccicp_multi_destroy", "ccicp_multi_device_count", "ccicp_multi_ctx", "ccicp_multi_last_error",
            "ccicp_shard_range", "ccicp_register_batch_multi", "ccicp_register_batch_multi_device", "ccicp_multi_sync",
-           "ccicp_multi_gather_kind", "ccicp_scans_upload", "ccicp_register_scan_pairs"]
+           "ccicp_multi_gather_kind", "ccicp_scans_upload", "ccicp_register_scan_pairs", "ccicp_scan_features"]
 
 _lib = None
 
@@ -89,6 +90,7 @@ def load():
     lib.ccicp_host_free.argtypes = [vp]
     lib.ccicp_get_launch_info.argtypes = [vp, C.POINTER(LaunchInfo)]
     lib.ccicp_get_diag_counts.argtypes = [vp, vp]
+    lib.ccicp_scan_features.argtypes = [vp, i32, vp, vp, i32, dbl, vp, vp]
     lib.ccicp_scans_upload.argtypes = [vp, i32, vp, vp]
     lib.ccicp_register_scan_pairs.argtypes = [vp, i32, i32, vp, vp, vp, C.POINTER(Params), vp]
     lib.ccicp_match_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
@@ -227,6 +229,17 @@ class Context:
 
     def sync(self, stream=None):
         self._check(self.lib.ccicp_stream_sync(self.h, stream or None))
+
+    def scan_features(self, xy, off, feat_k=5, feat_radius=0.5, want_normals=True):
+        """ccicp_scan_features: per-point (normal [n,2], curvature [n]) of clouds in the registration calls' CSR layout."""
+        off = np.ascontiguousarray(off, np.int32)
+        xy = np.ascontiguousarray(xy, np.float64).reshape(-1, 2)
+        n = len(xy)
+        nrm = np.zeros((max(n, 1), 2), np.float32) if want_normals else None
+        cur = np.zeros(max(n, 1), np.float32)
+        self._check(self.lib.ccicp_scan_features(self.h, (len(off) - 1) // 2, _ptr(xy), _ptr(off), int(feat_k), float(feat_radius),
+                                                 _ptr(nrm), _ptr(cur)))
+        return (nrm[:n] if want_normals else None), cur[:n]
 
     def scans_upload(self, scan_xy, scan_off):
         """ccicp_scans_upload: the ctx's scan table (float64 xy, int32 offsets [2*n_scans+1])."""

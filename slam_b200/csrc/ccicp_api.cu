@@ -40,6 +40,7 @@ struct ccicp_ctx {
   void* timed_stream = nullptr;
   DevBuf counter, scratch, all_results, workspace, diag, retry_list;
   DevBuf d_model, d_moff, d_scene, d_soff, d_init, d_out, d_corr;
+  DevBuf f_xy, f_off, f_nrm, f_curv;       // ccicp_scan_features
   DevBuf t_xy, t_off, t_mid, t_sid;        // scan table (ccicp_scans_upload) and the id lists of the last scan-pair call
   int32_t t_scans = 0, t_max_pts = 0, t_max_cells = 0;
   std::vector<int32_t> t_size;             // points per scan (host copy, argument checks)
@@ -95,6 +96,16 @@ bool is_pinned(const void* p) {
 
 int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
+// The dynamic shared-memory limit is per-FUNCTION state of the device: it is raised to the opt-in maximum once per
+// context creation, never per launch -- two host threads (one ctx each) launching pairs of different sizes would
+// otherwise race on it (one thread lowering the limit under the other's launch: "invalid argument").
+template <class K>
+bool allow_max_smem(K kernel, int max_optin) {
+  cudaFuncAttributes fa;
+  if (cudaFuncGetAttributes(&fa, kernel) != cudaSuccess) return false;
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin - (int)fa.sharedSizeBytes) == cudaSuccess;
+}
+
 // worst-case number of grid cells for a pair with at most max_model model points
 int max_cells_for(int max_model) {
   // one candidate per step of grid_side(): the smaller class just above each threshold, the rest in the other class
@@ -129,14 +140,16 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   const bool exact = (prm->flags & CCICP_F_EXACT_SUMS) != 0;
   const bool trim = (prm->flags & CCICP_F_TRIM) != 0;
   const bool diag = (prm->flags & CCICP_F_DIAG_COUNTS) != 0;
+  const bool curv = (prm->flags & CCICP_F_CURV_GATE) != 0;
+  if (curv && (exact || trim || diag || !(prm->curv_tol >= 0.0) || !(prm->feat_radius > 0.0) || prm->feat_k < 1)) return CCICP_E_INVALID;
   if (trim && (exact || !(prm->trim_frac > 0.0) || prm->trim_frac > 1.0)) return CCICP_E_INVALID;
   if (diag && (exact || trim)) return CCICP_E_INVALID;
-  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : diag ? icp_pair_diag_kernel : icp_pair_kernel;
-  auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : diag ? icp_pair_l2_diag_kernel : icp_pair_l2_kernel;
+  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : diag ? icp_pair_diag_kernel : curv ? icp_pair_curv_kernel : icp_pair_kernel;
+  auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : diag ? icp_pair_l2_diag_kernel : curv ? icp_pair_l2_curv_kernel : icp_pair_l2_kernel;
   cudaFuncAttributes fa_on;
   CK(cudaFuncGetAttributes(&fa_on, k_on));
   // problems whose default-mode solve meets a (nearly) rank-deficient H are re-run by the exact-order instantiation
-  const bool retry = !exact && !trim && !diag && !(prm->flags & CCICP_F_NO_EXACT_RETRY);
+  const bool retry = !exact && !trim && !diag && !curv && !(prm->flags & CCICP_F_NO_EXACT_RETRY);
   if (retry) {
     cudaFuncAttributes fa_ex;
     CK(cudaFuncGetAttributes(&fa_ex, icp_pair_exact_kernel));
@@ -144,21 +157,21 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   }
   // CCICP_F_TRIM: one u32 per scene point behind the carved working set (this iteration's squared distances, the keys
   // of the radix select)
-  const size_t warm_bytes = trim ? align_up((size_t)a.scap * 4, 128) : 0;
+  // CCICP_F_CURV_GATE: one float per model slot and per scene point (their curvatures) in the same place
+  const size_t warm_bytes = trim ? align_up((size_t)a.scap * 4, 128) : curv ? align_up(((size_t)a.mcap + a.scap) * 4, 128) : 0;
   size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false) + warm_bytes;
   const bool use_l2 = smem + fa_on.sharedSizeBytes > (size_t)ctx->max_smem_optin || ctx->force_l2;
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
   // large scans: the one-CTA-per-pair L2 variant by default; with CCICP_CLUSTER=1 one thread-block cluster per pair
   // (working sets of ~148 / kCluster pairs stay L2-resident: 0.23 GB instead of 4.6 GB of DRAM reads per wave, but the
   // cluster barriers cost more than the DRAM latency they remove: 7.1 k against 10.5 k pairs/s on C4)
-  const bool use_cluster = use_l2 && !exact && !trim && !diag && ctx->cluster;
+  const bool use_cluster = use_l2 && !exact && !trim && !diag && !curv && ctx->cluster;
   int occ = 0, n_clusters = 0;
   cudaLaunchConfig_t ccfg{};
   cudaLaunchAttribute cattr[1];
   if (use_cluster) {
     a.stage_cap = (ctx->stage_kb * 1024 / 6) & ~31;
     smem = (size_t)a.stage_cap * 6;
-    CK(cudaFuncSetAttribute(icp_pair_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cattr[0].id = cudaLaunchAttributeClusterDimension;
     cattr[0].val.clusterDim.x = kCluster; cattr[0].val.clusterDim.y = 1; cattr[0].val.clusterDim.z = 1;
     ccfg.gridDim = dim3((unsigned)(kCluster * ctx->sm_count), 1, 1); ccfg.blockDim = dim3(kThreadsCl, 1, 1);
@@ -171,10 +184,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     // what is left of the SM's 256 KB stays L1 cache for the workspace
     a.stage_cap = (ctx->stage_kb * 1024 / 6) & ~31;
     smem = (size_t)a.stage_cap * 6;
-    CK(cudaFuncSetAttribute(k_l2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_l2, threads, smem));
   } else {
-    CK(cudaFuncSetAttribute(k_on, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_on, threads, smem));
   }
   if (occ < 1) return CCICP_E_TOO_LARGE;
@@ -233,6 +244,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   a.n_pairs = n_pairs; a.n_seeds = n_seeds; a.seeds_per_item = seeds_per_item; a.items_per_pair = items_per_pair;
   a.max_iter = prm->max_iter; a.flags = prm->flags; a.min_delta = prm->min_delta; a.indist = prm->indist;
   a.trim_frac = prm->trim_frac;
+  a.curv_tol = prm->curv_tol; a.feat_radius = prm->feat_radius; a.feat_k = prm->feat_k;
   a.total_scene = total_scene; a.max_model = max_model;
   if (diag) {
     const bool fresh = ctx->diag.p == nullptr;
@@ -267,10 +279,8 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
     auto k2_l2 = icp_pair_l2_exact_kernel;
     int occ2 = 0;
     if (use_l2) {
-      CK(cudaFuncSetAttribute(k2_l2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, k2_l2, threads, smem));
     } else {
-      CK(cudaFuncSetAttribute(k2_on, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, k2_on, threads, smem));
     }
     if (occ2 < 1) return CCICP_E_TOO_LARGE;
@@ -342,6 +352,8 @@ void ccicp_default_params(ccicp_params* p) {
   p->reject_dist = 0.0;        // off; graph_slam uses 10 m / 0.2 rad (graphSlamTools.h:35-36)
   p->reject_rot = 0.0;
   p->trim_frac = 1.0;          // off (CCICP_F_TRIM is an extra the reference does not have)
+  p->curv_tol = 0.05;          // CCICP_F_CURV_GATE (an extra, off by default)
+  p->feat_radius = 0.5; p->feat_k = 5; p->reserved = 0;
 }
 
 int ccicp_create(ccicp_ctx** out, int device) {
@@ -372,6 +384,11 @@ int ccicp_create(ccicp_ctx** out, int device) {
   bool ok = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
   for (auto& ks : ctx->kstream) ok = ok && cudaStreamCreateWithFlags(&ks, cudaStreamNonBlocking) == cudaSuccess;
   for (auto& ev : ctx->chunk_ev) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+  const int mo = ctx->max_smem_optin;
+  ok = ok && allow_max_smem(icp_pair_kernel, mo) && allow_max_smem(icp_pair_l2_kernel, mo) && allow_max_smem(icp_pair_exact_kernel, mo) &&
+       allow_max_smem(icp_pair_l2_exact_kernel, mo) && allow_max_smem(icp_pair_trim_kernel, mo) && allow_max_smem(icp_pair_l2_trim_kernel, mo) &&
+       allow_max_smem(icp_pair_diag_kernel, mo) && allow_max_smem(icp_pair_l2_diag_kernel, mo) && allow_max_smem(icp_pair_curv_kernel, mo) &&
+       allow_max_smem(icp_pair_l2_curv_kernel, mo) && allow_max_smem(icp_pair_cluster_kernel, mo);
   if (!ok) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
   *out = ctx;
   return CCICP_OK;
@@ -381,7 +398,7 @@ int ccicp_destroy(ccicp_ctx* ctx) {
   if (!ctx) return CCICP_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->t_xy, &ctx->t_off, &ctx->t_mid, &ctx->t_sid, &ctx->retry_list, &ctx->diag, &ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
+  DevBuf* bufs[] = {&ctx->f_xy, &ctx->f_off, &ctx->f_nrm, &ctx->f_curv, &ctx->t_xy, &ctx->t_off, &ctx->t_mid, &ctx->t_sid, &ctx->retry_list, &ctx->diag, &ctx->counter, &ctx->scratch, &ctx->all_results, &ctx->workspace, &ctx->d_model, &ctx->d_moff, &ctx->d_scene,
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
                     &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_tile_base, &ctx->c_tile_seg, &ctx->c_group_base, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
                     &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
@@ -546,6 +563,39 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   else { for (auto& ks : ctx->kstream) CK(cudaStreamSynchronize(ks)); }
   if (out_dst != out) memcpy(out, out_dst, n_out * sizeof(ccicp_result));
   ctx->timed_copies = true;
+  return CCICP_OK;
+}
+
+// ---- per-point features (north_star extra) -------------------------------------------------------------------------
+int ccicp_scan_features(ccicp_ctx* ctx, int32_t n_clouds, const double* xy, const int32_t* off, int32_t feat_k,
+                        double feat_radius, float* normal_xy, float* curvature) {
+  if (!ctx || n_clouds < 0 || feat_k < 1 || !(feat_radius > 0.0)) return CCICP_E_INVALID;
+  if (n_clouds == 0) return CCICP_OK;
+  if (!off || off[0] != 0 || !offsets_ok(off, n_clouds) || !curvature) return CCICP_E_INVALID;
+  const int64_t n = off[2 * (size_t)n_clouds];
+  if (n == 0) return CCICP_OK;
+  if (!xy) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  int rc;
+  const size_t off_bytes = (2 * (size_t)n_clouds + 1) * 4;
+  if ((rc = reserve(ctx, ctx->f_xy, (size_t)n * 16))) return rc;
+  if ((rc = reserve(ctx, ctx->f_off, off_bytes))) return rc;
+  if ((rc = reserve(ctx, ctx->f_nrm, (size_t)n * 8))) return rc;
+  if ((rc = reserve(ctx, ctx->f_curv, (size_t)n * 4))) return rc;
+  CK(cudaMemcpyAsync(ctx->f_xy.p, xy, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->f_off.p, off, off_bytes, cudaMemcpyHostToDevice, st));
+  CK(cudaEventRecord(ctx->ev[2], st));
+  feat::scan_features_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const double2*)ctx->f_xy.p, (const int32_t*)ctx->f_off.p,
+                                                                          2 * n_clouds, (int)n, feat_k, feat_radius * feat_radius,
+                                                                          normal_xy ? (float2*)ctx->f_nrm.p : nullptr, (float*)ctx->f_curv.p);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(ctx->ev[3], st));
+  ctx->timed = true; ctx->timed_copies = false; ctx->timed_stream = (void*)st;
+  ctx->info.n_launches = 1; ctx->info.kernel_variant = 5; ctx->info.block = 256; ctx->info.grid = (int)((n + 255) / 256);
+  if (normal_xy) CK(cudaMemcpyAsync(normal_xy, ctx->f_nrm.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(curvature, ctx->f_curv.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
   return CCICP_OK;
 }
 

@@ -52,6 +52,7 @@ struct IcpArgs {
   int32_t max_iter; uint32_t flags;
   double min_delta, indist;
   double trim_frac;              // CCICP_F_TRIM: fraction of the gated correspondences kept per iteration
+  double curv_tol, feat_radius; int32_t feat_k, pad_feat;   // CCICP_F_CURV_GATE: |curvature difference| allowed, feature neighbourhood
   int64_t total_scene;           // corr_idx seed stride (scene points in the whole batch)
   int32_t mcap, scap, ccap;      // shared-memory capacities: model points, scene points, cells
   int32_t max_model;             // scratch sizing

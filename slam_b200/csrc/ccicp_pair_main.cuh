@@ -7,6 +7,7 @@
 #define CCICP_SOLVE_ALL 0
 #endif
 #include "exact_solve.cuh"
+#include "features.cuh"
 
 namespace ccicp {
 
@@ -271,7 +272,7 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, int ns, int 
   }
 }
 
-template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false, bool kDiag = false>
+template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false, bool kDiag = false, bool kCurv = false>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
@@ -289,9 +290,18 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
     trim_keys = (uint32_t*)(base + workset_bytes(a.mcap, a.scap, a.ccap, kGlobal));
     if (!kGlobal) __builtin_assume(__isShared(trim_keys));
   }
+  // kCurv (CCICP_F_CURV_GATE): curvature of every model point (by sorted slot) and of every scene point, behind the
+  // carved working set; computed once per pair from the FP64 inputs (features.cuh)
+  float* mcurv = nullptr; float* scurv = nullptr;
+  if constexpr (kCurv) {
+    mcurv = (float*)(base + workset_bytes(a.mcap, a.scap, a.ccap, kGlobal));
+    scurv = mcurv + a.mcap;
+    if (!kGlobal) { __builtin_assume(__isShared(mcurv)); __builtin_assume(__isShared(scurv)); }
+  }
+  const float ctol = kCurv ? (float)a.curv_tol : 0.0f;
   const int tid = threadIdx.x;
   const float gate_f = __double2float_ru(a.indist);
-  const bool replay_on = !(a.flags & CCICP_F_NO_TIE_REPLAY);
+  const bool replay_on = !(a.flags & CCICP_F_NO_TIE_REPLAY) && !kCurv;      // curvature-gated ties: lowest model index (below)
   // a.item_list (exact-order re-run of flagged problems): one listed (pair, seed) problem per work item, the count
   // was left on the device by collect_retry_kernel
   const bool listed = a.item_list != nullptr;
@@ -333,6 +343,24 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
         for (int i = tid; i < ns; i += kThreads) dst[i] = __ldg(src + i);
         // each thread only ever reads back the scene points it loaded itself
       }
+      if constexpr (kCurv) {
+        const double r2 = a.feat_radius * a.feat_radius;
+        const double2* msrc = (const double2*)a.model_xy + m0;
+        for (int i = tid; i < nmGA + nmNGA; i += kThreads) {
+          const bool nga = i >= nmGA;
+          if (s.grid[nga].G == 0) continue;                  // class never searched: its points have no slot
+          float c, nx, ny;
+          feat::point_feature(msrc, i, nga ? nmGA : 0, nga ? nmGA + nmNGA : nmGA, a.feat_k, r2, c, nx, ny);
+          mcurv[s.kinv[i]] = c;
+        }
+        for (int i = tid; i < ns; i += kThreads) {
+          const bool nga = i >= nsGA;
+          float c, nx, ny;
+          feat::point_feature(src, i, nga ? nsGA : 0, nga ? ns : nsGA, a.feat_k, r2, c, nx, ny);
+          scurv[i] = c;
+        }
+        __syncthreads();
+      }
     }
 
     for (int seed = seed0; seed < seed1; seed++) {
@@ -373,7 +401,19 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               float best; int bslot, tie;
               unsigned start = s.slots[i];
               if constexpr (kTrim) { if (start == kNoSlot) start = trim_keys[i] & 0xFFFFu; }
-              nn_search<kGlobal, kDiag>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
+              if constexpr (kCurv) {
+                const float qc = scurv[i];
+                nn_search<kGlobal, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
+                if (tie) {     // several compatible model points at the float minimum (rare): the lowest model index wins
+                  const QPack q2 = pack_query(qx, qy);
+                  int bo = 0x7fffffff;
+                  for (int j = s.cstart[g.base]; j < s.cstart[g.base + g.G * g.G]; j++)
+                    if (!(fabsf(mcurv[j] - qc) > ctol) && dist2(s.mpts[j], q2) == best && (int)s.morig[j] < bo) { bo = s.morig[j]; bslot = j; }
+                  tie = 0;
+                }
+              } else {
+                nn_search<kGlobal, kDiag>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
+              }
               if (kDiag) diag_queries++;
               if (bslot >= 0 && (double)best < a.indist) {
                 slot = (unsigned)bslot;
@@ -526,7 +566,18 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
             unsigned slot = kNoSlot;
             if (g.G > 0) {
               float best; int bslot, tie;
-              nn_search<kGlobal, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
+              if constexpr (kCurv) {
+                const float qc = scurv[i];
+                nn_search<kGlobal, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals, mcurv, qc, ctol);
+                if (tie) {
+                  const QPack q2 = pack_query(qx, qy);
+                  int bo = 0x7fffffff;
+                  for (int j = s.cstart[g.base]; j < s.cstart[g.base + g.G * g.G]; j++)
+                    if (!(fabsf(mcurv[j] - qc) > ctol) && dist2(s.mpts[j], q2) == best && (int)s.morig[j] < bo) { bo = s.morig[j]; bslot = j; }
+                }
+              } else {
+                nn_search<kGlobal, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
+              }
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
               if constexpr (kTrim) trim_keys[i] = slot != kNoSlot ? __float_as_uint(best) : 0xFFFFFFFFu;
             } else if constexpr (kTrim) trim_keys[i] = 0xFFFFFFFFu;
@@ -624,6 +675,14 @@ __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_dia
 }
 __global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_diag_kernel(const IcpArgs a) {
   icp_pair_body<kThreadsL2, true, false, false, true>(a);
+}
+
+// CCICP_F_CURV_GATE instantiations (north_star extra: curvature-gated correspondence search)
+__global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_curv_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsOnChip, false, false, false, false, true>(a);
+}
+__global__ void __launch_bounds__(kThreadsL2, 1) icp_pair_l2_curv_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsL2, true, false, false, false, true>(a);
 }
 
 // CCICP_F_EXACT_SUMS instantiations (separate kernels so the default ones carry none of their register pressure).

@@ -142,9 +142,12 @@ NN_D float dist2(const float2 p, const QPack& q) {
 // kDense (L2 variant, densely sampled scans): doubling probe blocks + chord pruning; the on-chip variant keeps the
 // cheaper home cell / 3x3 probes and a bounding-box sweep (measured: the extra arithmetic costs 4 % on 1081-beam pairs).
 // kDiag: count the distance evaluations into `evals` (diagnostics instantiation only).
-template <bool kDense, bool kDiag = false>
+// kCurv (CCICP_F_CURV_GATE, an extra without reference counterpart): a candidate whose curvature mcurv[j] differs from
+// the query's `qc` by more than `ctol` is not a candidate at all (NaN = no feature: compatible with everything).
+template <bool kDense, bool kDiag = false, bool kCurv = false>
 NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, float qx, float qy, float gate_f,
-                    unsigned warm, float& best, int& bslot, int& tie, int& evals) {
+                    unsigned warm, float& best, int& bslot, int& tie, int& evals, const float* mcurv = nullptr,
+                    float qc = 0.0f, float ctol = 0.0f) {
   best = CUDART_INF_F; bslot = -1;
   float second = CUDART_INF_F;      // second smallest distance seen (with multiplicity): tie <=> second == best
   const int G = g.G;
@@ -218,7 +221,8 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
           for (int k = 0; k < 3; k++) {
 #pragma unroll kRowUnroll
             for (int j = jb[k]; j < je[k]; j++) {
-              const float d = dist2(mpts[j], q2);
+              float d = dist2(mpts[j], q2);
+              if (kCurv) d = fabsf(mcurv[j] - qc) > ctol ? CUDART_INF_F : d;
               bslot = d < best ? j : bslot;
               second = fminf(second, fmaxf(d, best));
               best = fminf(best, d);
@@ -231,7 +235,8 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
             off = t < n01 ? o1 : off;
             off = t < n0 ? j0 : off;
             const int j = t + off;
-            const float d = dist2(mpts[j], q2);
+            float d = dist2(mpts[j], q2);
+            if (kCurv) d = fabsf(mcurv[j] - qc) > ctol ? CUDART_INF_F : d;
             bslot = d < best ? j : bslot;
             second = fminf(second, fmaxf(d, best));
             best = fminf(best, d);

@@ -24,13 +24,13 @@ def test_every_declared_symbol_is_exported():
     assert len(names) >= 12 and set(names) == set(capi.SYMBOLS)
     for n in names:
         assert hasattr(lib, n), n
-    assert lib.ccicp_abi_version() == 4
+    assert lib.ccicp_abi_version() == 5
 
 
 def test_struct_layouts():
     assert capi.RESULT_DTYPE.itemsize == 160
     assert capi.RESULT_DTYPE.fields["info"][1] == 48 and capi.RESULT_DTYPE.fields["num_corr"][1] == 136
-    assert C.sizeof(capi.Params) == 64
+    assert C.sizeof(capi.Params) == 88
     p = capi.default_params()
     assert (p.max_iter, p.min_delta, p.indist, p.flags) == (20, 1e-6, 5.0, 0)      # icp.cpp:27, icpTools.cpp:188
 
