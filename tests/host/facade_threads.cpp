@@ -24,6 +24,7 @@ static Answer run_pair(const double* m, const int32_t* c, const double* s) {
   icp.setMaxIterations(30); icp.setMinDeltaParam(-2.0);
   icp.fit(const_cast<double*>(s), const_cast<double*>(s) + 2 * c[2], c[2], c[3], rot, trans, 5, 0);
   Answer a;
+  std::memset(&a, 0, sizeof(a));           // (padding after `n`: the answers are compared with memcmp)
   a.t0 = trans.val[0][0]; a.t1 = trans.val[1][0]; a.yaw = std::atan2(rot.val[1][0], rot.val[0][0]);
   a.n = icp.getNumberCorrespondences();
   icp.getEdgeWeight(a.eW);

@@ -22,7 +22,7 @@ def test_features_match_the_cpu_statement(ctx):
             np.testing.assert_allclose(nrm, wn, rtol=0, atol=2e-6)
     nrm, cur = ctx.scan_features(b.model_xy, b.model_off)
     ok = ~np.isnan(cur)
-    assert ok.mean() > 0.9 and np.median(cur[ok]) < 0.01 and cur[ok].max() > 0.05        # walls are flat, corners are not
+    assert ok.mean() > 0.9 and np.median(cur[ok]) < 0.05 and cur[ok].max() > 0.2         # walls are flat (1 cm range noise), corners are not
     assert np.abs(np.linalg.norm(nrm[ok & (np.abs(nrm).sum(1) > 0)], axis=1) - 1).max() < 1e-6
 
 
