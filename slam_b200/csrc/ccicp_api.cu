@@ -14,6 +14,7 @@
 #include "pose_math.h"
 #include "classify.cuh"
 #include "lum.cuh"
+#include "lum_grid.cuh"
 
 using namespace ccicp;
 
@@ -45,7 +46,7 @@ struct ccicp_ctx {
   int32_t t_scans = 0, t_max_pts = 0, t_max_cells = 0;
   std::vector<int32_t> t_size;             // points per scan (host copy, argument checks)
   DevBuf c_keys, c_vals, c_keys_tmp, c_vals_tmp, c_hist, c_bitmap, c_tile_base, c_tile_seg, c_group_base;            // classification scratch
-  DevBuf l_src, l_soff, l_tgt, l_toff, l_dist, l_idx, l_info, l_num, l_status;   // Lu-Milios edge information
+  DevBuf l_src, l_soff, l_tgt, l_toff, l_dist, l_idx, l_info, l_num, l_status, l_head, l_next, l_tabo;   // Lu-Milios edge information
   DevBuf c_xyz, c_off, c_out_xyz, c_out_ga, c_out_src, c_out_cnt;             // classification, host-buffer path
   ccicp_launch_info info{};
   std::string last_err;
@@ -402,7 +403,7 @@ int ccicp_destroy(ccicp_ctx* ctx) {
                     &ctx->d_soff, &ctx->d_init, &ctx->d_out, &ctx->d_corr, &ctx->c_keys, &ctx->c_vals, &ctx->c_keys_tmp,
                     &ctx->c_vals_tmp, &ctx->c_hist, &ctx->c_bitmap, &ctx->c_tile_base, &ctx->c_tile_seg, &ctx->c_group_base, &ctx->c_xyz, &ctx->c_off, &ctx->c_out_xyz,
                     &ctx->c_out_ga, &ctx->c_out_src, &ctx->c_out_cnt, &ctx->l_src, &ctx->l_soff, &ctx->l_tgt, &ctx->l_toff,
-                    &ctx->l_dist, &ctx->l_idx, &ctx->l_info, &ctx->l_num, &ctx->l_status};
+                    &ctx->l_dist, &ctx->l_idx, &ctx->l_info, &ctx->l_num, &ctx->l_status, &ctx->l_head, &ctx->l_next, &ctx->l_tabo};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   if (ctx->h_init.p) cudaFreeHost(ctx->h_init.p);
   if (ctx->h_out.p) cudaFreeHost(ctx->h_out.p);
@@ -825,12 +826,45 @@ int ccicp_edge_information_lum(ccicp_ctx* ctx, int32_t n_edges, const float* sou
   a.info = (double*)ctx->l_info.p; a.num_corr = (int32_t*)ctx->l_num.p; a.status = (uint32_t*)ctx->l_status.p;
   a.max_corr_distance = max_corr_distance; a.n_edges = n_edges;
   const int grid = n_edges < ctx->sm_count * 4 ? n_edges : ctx->sm_count * 4;
+  // clouds beyond one shared-memory tile: nearest neighbours through the 3-D hash grid (lum_grid.cuh) instead of the
+  // O(n * m) sweep (CCICP_LUM_GRID=0 / 1 forces either)
+  int max_t = 0;
+  for (int32_t e = 0; e < n_edges; e++) max_t = std::max(max_t, target_off[e + 1] - target_off[e]);
+  bool use_grid = max_t > lum::kTile;
+  { const char* ev = getenv("CCICP_LUM_GRID"); if (ev) use_grid = ev[0] == '1'; }
+  int n_launches = 1;
   CK(cudaEventRecord(ctx->ev[2], st));
-  lum::lum_edge_kernel<<<grid, lum::kThreads, 0, st>>>(a);
+  if (use_grid && ns > 0 && nt > 0) {
+    std::vector<int64_t> tabo((size_t)n_edges + 1, 0);
+    for (int32_t e = 0; e < n_edges; e++) {
+      int64_t h = 64;
+      while (h < 2 * (int64_t)(target_off[e + 1] - target_off[e])) h <<= 1;
+      tabo[e + 1] = tabo[e] + h;
+    }
+    if ((rc = reserve(ctx, ctx->l_tabo, tabo.size() * 8))) return rc;
+    if ((rc = reserve(ctx, ctx->l_head, (size_t)tabo[n_edges] * 4))) return rc;
+    if ((rc = reserve(ctx, ctx->l_next, nt * 4 + 16))) return rc;
+    CK(cudaMemcpyAsync(ctx->l_tabo.p, tabo.data(), tabo.size() * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));                     // tabo is a local
+    CK(cudaMemsetAsync(ctx->l_head.p, 0xFF, (size_t)tabo[n_edges] * 4, st));
+    lum::GridArgs g{};
+    g.source_xyz = a.source_xyz; g.source_off = a.source_off; g.target_xyz = a.target_xyz; g.target_off = a.target_off;
+    g.table_off = (const int64_t*)ctx->l_tabo.p; g.head = (int32_t*)ctx->l_head.p; g.next = (int32_t*)ctx->l_next.p;
+    g.nn_dist = a.nn_dist; g.nn_idx = a.nn_idx; g.n_edges = n_edges;
+    g.inv_h = (float)(1.0 / (max_corr_distance * 1.001));
+    g.gate = (float)(max_corr_distance * max_corr_distance);
+    if ((double)g.gate < max_corr_distance * max_corr_distance) g.gate = nextafterf(g.gate, INFINITY);
+    lum::lum_grid_build_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(g, (int)nt);
+    lum::lum_grid_nn_kernel<<<(unsigned)((ns + 255) / 256), 256, 0, st>>>(g, (int)ns);
+    lum::lum_edge_kernel<true><<<grid, lum::kThreads, 0, st>>>(a);
+    n_launches = 3;
+  } else {
+    lum::lum_edge_kernel<false><<<grid, lum::kThreads, 0, st>>>(a);
+  }
   CK(cudaGetLastError());
   CK(cudaEventRecord(ctx->ev[3], st));
   ctx->timed = true; ctx->timed_copies = false; ctx->timed_stream = (void*)st;
-  ctx->info.n_launches = 1; ctx->info.grid = grid; ctx->info.block = lum::kThreads; ctx->info.kernel_variant = 3;
+  ctx->info.n_launches = n_launches; ctx->info.grid = grid; ctx->info.block = lum::kThreads; ctx->info.kernel_variant = use_grid ? 6 : 3;
   CK(cudaMemcpyAsync(info, ctx->l_info.p, (size_t)n_edges * 36 * 8, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(num_corr, ctx->l_num.p, (size_t)n_edges * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(status, ctx->l_status.p, (size_t)n_edges * 4, cudaMemcpyDeviceToHost, st));

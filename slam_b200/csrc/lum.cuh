@@ -90,6 +90,8 @@ __device__ __forceinline__ int first_equal(const float3& p, const float* tx, con
   return g + 3;
 }
 
+// kHaveNN: nn_dist / nn_idx were filled by the hash-grid search (lum_grid.cuh); the brute-force sweep is skipped.
+template <bool kHaveNN>
 __global__ void __launch_bounds__(kThreads) lum_edge_kernel(const Args a) {
   __shared__ __align__(16) float tx[kTile], ty[kTile], tz[kTile];
   __shared__ double red[kWarps * kSums];
@@ -101,8 +103,8 @@ __global__ void __launch_bounds__(kThreads) lum_edge_kernel(const Args a) {
     const int t0 = a.target_off[e], nt = a.target_off[e + 1] - t0;
     const float3* src = (const float3*)a.source_xyz + s0;
     // ---- exact nearest target point of every source point
-    for (int i = tid; i < ns; i += kThreads) { a.nn_dist[s0 + i] = CUDART_INF_F; a.nn_idx[s0 + i] = -1; }
-    for (int tb = 0; tb < nt; tb += kTile) {
+    if (!kHaveNN) for (int i = tid; i < ns; i += kThreads) { a.nn_dist[s0 + i] = CUDART_INF_F; a.nn_idx[s0 + i] = -1; }
+    for (int tb = 0; tb < (kHaveNN ? 0 : nt); tb += kTile) {
       const int m = min(kTile, nt - tb);
       __syncthreads();
       for (int j = tid; j < m; j += kThreads) {

@@ -50,3 +50,35 @@ def test_rejection_rule_restatement():
     assert lum_port.edge_is_rejected((0, 0, 0), (10.5, 0, 0))
     assert lum_port.edge_is_rejected((0, 0, 3.1), (0, 0, -3.0)) is False       # wraps to 0.18 rad
     assert lum_port.edge_is_rejected((0, 0, 3.0), (0, 0, -3.0))                # wraps to 0.28 rad
+
+
+def test_large_clouds_go_through_the_hash_grid(ctx):
+    """Clouds beyond one shared-memory tile (the voxel-filtered Velodyne clouds of graph_slam have tens of thousands of
+    points): nearest neighbours come from the 3-D hash grid (lum_grid.cuh) and must give the same information matrix
+    as the exhaustive sweep and as the oracle."""
+    import os
+    from slam_b200 import capi
+    pairs = [cloud_pair(11, 20000), cloud_pair(12, 6000), cloud_pair(13, 300)]
+    src, tgt = [p[0] for p in pairs], [p[1] for p in pairs]
+    info, num, st = ctx.edge_information_lum(src, tgt, 0.75)
+    assert ctx.launch_info().kernel_variant == 6 and ctx.launch_info().n_launches == 3
+    os.environ["CCICP_LUM_GRID"] = "0"
+    try:
+        info0, num0, st0 = ctx.edge_information_lum(src, tgt, 0.75)
+    finally:
+        del os.environ["CCICP_LUM_GRID"]
+    assert ctx.launch_info().kernel_variant == 3
+    assert np.array_equal(num, num0) and np.array_equal(st, st0) and np.array_equal(info, info0)     # same pairs, same sums
+    wi, wn, ws = lum_port.edge_information(pairs[1][0], pairs[1][1], 0.75)
+    assert num[1] == wn and st[1] == ws
+    np.testing.assert_allclose(info[1], wi, rtol=2e-5, atol=2e-5 * np.abs(wi).max())
+    # duplicates and exact ties: lowest target index, like the sweep
+    t = np.repeat(cloud_pair(14, 3000)[1], 2, 0)
+    s = t[::3] + np.float32(0.01)
+    a, na, sa = ctx.edge_information_lum([s], [t], 0.75)
+    os.environ["CCICP_LUM_GRID"] = "0"
+    try:
+        b, nb, sb = ctx.edge_information_lum([s], [t], 0.75)
+    finally:
+        del os.environ["CCICP_LUM_GRID"]
+    assert np.array_equal(a, b) and np.array_equal(na, nb)
