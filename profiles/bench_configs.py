@@ -59,6 +59,8 @@ def main():
         run(ctx, "C5 256 seeds best-of", b, prm5, n_seeds=S, init=init, reps=2)
     if "lum" in which:
         bench_lum(ctx, pairs or 592)
+    if "lumbig" in which:      # the size class graph_slam really has: voxel-filtered Velodyne clouds
+        bench_lum(ctx, pairs or 64, pts=30000)
     if "classify" in which:
         bench_classify(ctx, pairs or 256)
     ctx.close()

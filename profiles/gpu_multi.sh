@@ -10,7 +10,7 @@ for n in 1 2 4 8; do
   if [ $n -eq 1 ]; then python profiles/h2d_ceiling.py; else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 profiles/h2d_ceiling.py; fi
 done > $out/h2d_ceiling.jsonl 2> $out/h2d_ceiling.err
 cat $out/h2d_ceiling.jsonl
-for n in 2 4 8; do
+for n in ${BENCH_NS:-2 4 8}; do
   [ $n -gt $N ] && break
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $n --steps 10 --warmup 3 > $out/bench_${n}gpu.json 2> $out/bench_${n}gpu.err
   python -c "
