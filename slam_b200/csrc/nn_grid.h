@@ -132,6 +132,25 @@ NN_D float dist2(const float2 p, const QPack& q) {
 #endif
 }
 
+// Upper bound of sqrt(x) for the search radius: sqrt.approx (1 ulp) -- the callers multiply by 1.00001, far above that
+// error, so the IEEE round-up sequence of __fsqrt_ru (10 instructions) is not needed.  Host build: the exact form.
+NN_D float sqrt_up(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return __fsqrt_ru(x);
+#endif
+}
+NN_D int floor_int(float x) {      // (int)floorf(x) as one conversion
+#if defined(__CUDA_ARCH__)
+  return __float2int_rd(x);
+#else
+  return (int)floorf(x);
+#endif
+}
+
 // ---- exact float nearest neighbour over one class grid: row sweep -------------------------------------------------
 // Row sweep in chunks of three grid rows.  An upper bound `best` comes from the previous iteration's match (warm
 // start) or, failing that, from probing the home cell and then the 3x3 block.  A row is cut to the cell span that can
@@ -173,15 +192,15 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
     float su = 0.0f;
     if (r >= 0) {
       if (best < CUDART_INF_F || (kDense ? (float)r > gate_cells : r > 1)) { r = -1; continue; }
-      const int cx = (int)floorf(ux), cy = (int)floorf(uy);
+      const int cx = floor_int(ux), cy = floor_int(uy);
       xa = cx - r; xb = cx + r; ya = cy - r; yb = cy + r;
     } else {
       // keep only the bound: restart from the next float above B so every point is tested exactly once
       best = __int_as_float(__float_as_int(best) + (best < CUDART_INF_F ? 1 : 0));
       second = CUDART_INF_F; bslot = -1;
-      su = __fsqrt_ru(fminf(best, gate_f)) * inv_h * 1.00001f + slop;   // search radius in cells, rounded up
-      xa = (int)floorf(ux - su); xb = (int)floorf(ux + su);
-      ya = (int)floorf(uy - su); yb = (int)floorf(uy + su);
+      su = sqrt_up(fminf(best, gate_f)) * inv_h * 1.00001f + slop;   // search radius in cells, rounded up
+      xa = floor_int(ux - su); xb = floor_int(ux + su);
+      ya = floor_int(uy - su); yb = floor_int(uy + su);
     }
     xa = max(xa, 0); xb = min(xb, G - 1); ya = max(ya, 0); yb = min(yb, G - 1);
     if (xa <= xb) {
@@ -189,8 +208,8 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
       for (int y = ya; y <= yb; y += 3) {
         int xs = xa, xe = xb;
         if (!kDense && y > ya) {            // later chunks: shrink the column span to the current bound
-          const float s2 = __fsqrt_ru(fminf(best, gate_f)) * inv_h * 1.00001f + slop;
-          xa = max(xa, (int)floorf(ux - s2)); xb = min(xb, (int)floorf(ux + s2));
+          const float s2 = sqrt_up(fminf(best, gate_f)) * inv_h * 1.00001f + slop;
+          xa = max(xa, floor_int(ux - s2)); xb = min(xb, floor_int(ux + s2));
           if (xa > xb) break;
           xs = xa; xe = xb;
         }
