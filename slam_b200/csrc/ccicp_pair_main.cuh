@@ -272,13 +272,6 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, int ns, int 
   }
 }
 
-// L2 variant: copy the first `cap` sorted model points into the (otherwise idle) tie-replay staging area
-template <int kThreads>
-__device__ __forceinline__ void fill_mpts_cache(float2* sh, const float2* mpts, int cap, int tid) {
-  for (int i = tid; i < cap; i += kThreads) sh[i] = mpts[i];
-  __syncthreads();
-}
-
 template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false, bool kDiag = false, bool kCurv = false>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
@@ -313,8 +306,6 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   // was left on the device by collect_retry_kernel
   const bool listed = a.item_list != nullptr;
   const int n_items = listed ? *a.item_count : a.n_pairs * a.items_per_pair;
-  MptsSplit msplit{(const float2*)smem_raw, nullptr, 0};      // kGlobal only
-  __builtin_assume(__isShared(msplit.sh));
   int diag_evals = 0, diag_queries = 0, diag_inliers = 0;      // kDiag only (dead otherwise)
 
   for (;;) {
@@ -347,9 +338,6 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
       const double2* src = (const double2*)a.scene_xy + s0;
       if (kGlobal) {
         s.scene = src;             // read the (L2-resident) input in place every iteration
-        msplit.cap = min(nmGA + nmNGA, (int)(((size_t)a.stage_cap * 6) / sizeof(float2)));
-        msplit.gl = s.mpts;
-        fill_mpts_cache<kThreads>((float2*)smem_raw, s.mpts, msplit.cap, tid);
       } else {
         double2* dst = (double2*)s.region0;
         for (int i = tid; i < ns; i += kThreads) dst[i] = __ldg(src + i);
@@ -415,8 +403,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               if constexpr (kTrim) { if (start == kNoSlot) start = trim_keys[i] & 0xFFFFu; }
               if constexpr (kCurv) {
                 const float qc = scurv[i];
-                if constexpr (kGlobal) nn_search<true, false, true, MptsSplit>(msplit, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
-                else nn_search<false, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
+                nn_search<kGlobal, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
                 if (tie) {     // several compatible model points at the float minimum (rare): the lowest model index wins
                   const QPack q2 = pack_query(qx, qy);
                   int bo = 0x7fffffff;
@@ -425,8 +412,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
                   tie = 0;
                 }
               } else {
-                if constexpr (kGlobal) nn_search<true, kDiag, false, MptsSplit>(msplit, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
-                else nn_search<false, kDiag>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
+                nn_search<kGlobal, kDiag>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
               }
               if (kDiag) diag_queries++;
               if (bslot >= 0 && (double)best < a.indist) {
@@ -450,7 +436,6 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
           if (any_tie) {                         // rare: replay the reference kd-tree for the tied queries
             if (kGlobal) {
               replay_ties_coop<kThreads>(a, s, Rt, ns, nsGA, tid, smem_raw, a.stage_cap, (float*)rtprev_s + 16, s.scene, nullptr);
-              fill_mpts_cache<kThreads>((float2*)smem_raw, s.mpts, msplit.cap, tid);      // the replay staged its nodes there
             } else {
               // On chip the whole CTA replays too (one thread per class used to: 0.1-0.3 ms for the first tie of a pair,
               // and a tie in one of the last pairs of a launch is the kernel's tail -- the 14 replays of the C2 batch
@@ -583,8 +568,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               float best; int bslot, tie;
               if constexpr (kCurv) {
                 const float qc = scurv[i];
-                if constexpr (kGlobal) nn_search<true, false, true, MptsSplit>(msplit, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals, mcurv, qc, ctol);
-                else nn_search<false, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals, mcurv, qc, ctol);
+                nn_search<kGlobal, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals, mcurv, qc, ctol);
                 if (tie) {
                   const QPack q2 = pack_query(qx, qy);
                   int bo = 0x7fffffff;
@@ -592,8 +576,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
                     if (!(fabsf(mcurv[j] - qc) > ctol) && dist2(s.mpts[j], q2) == best && (int)s.morig[j] < bo) { bo = s.morig[j]; bslot = j; }
                 }
               } else {
-                if constexpr (kGlobal) nn_search<true, false, false, MptsSplit>(msplit, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
-                else nn_search<false, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
+                nn_search<kGlobal, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
               }
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
               if constexpr (kTrim) trim_keys[i] = slot != kNoSlot ? __float_as_uint(best) : 0xFFFFFFFFu;

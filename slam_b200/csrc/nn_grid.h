@@ -151,13 +151,6 @@ NN_D int floor_int(float x) {      // (int)floorf(x) as one conversion
 #endif
 }
 
-// L2 variant: the first `cap` sorted model points are also kept in the CTA's shared memory (the staging area of the tie
-// replay, idle otherwise); slots are sorted by cell, so the candidates of one query come almost always from one side.
-struct MptsSplit {
-  const float2* sh; const float2* gl; int cap;
-  NN_D float2 operator[](int j) const { return j < cap ? sh[j] : gl[j]; }
-};
-
 // ---- exact float nearest neighbour over one class grid: row sweep -------------------------------------------------
 // Row sweep in chunks of three grid rows.  An upper bound `best` comes from the previous iteration's match (warm
 // start) or, failing that, from probing the home cell and then the 3x3 block.  A row is cut to the cell span that can
@@ -170,9 +163,8 @@ struct MptsSplit {
 // kDiag: count the distance evaluations into `evals` (diagnostics instantiation only).
 // kCurv (CCICP_F_CURV_GATE, an extra without reference counterpart): a candidate whose curvature mcurv[j] differs from
 // the query's `qc` by more than `ctol` is not a candidate at all (NaN = no feature: compatible with everything).
-// MP: anything indexable to float2 -- a plain pointer, or MptsSplit below.
-template <bool kDense, bool kDiag = false, bool kCurv = false, class MP = const float2*>
-NN_D void nn_search(MP mpts, const uint16_t* cstart, const GridP& g, float qx, float qy, float gate_f,
+template <bool kDense, bool kDiag = false, bool kCurv = false>
+NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, float qx, float qy, float gate_f,
                     unsigned warm, float& best, int& bslot, int& tie, int& evals, const float* mcurv = nullptr,
                     float qc = 0.0f, float ctol = 0.0f) {
   best = CUDART_INF_F; bslot = -1;
