@@ -31,6 +31,7 @@ import time
 
 import numpy as np
 
+T_START = time.perf_counter()      # the whole run's wall clock is reported as bench_wall_s
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -617,6 +618,7 @@ def main():
     line = gpu_arm(args, rank, world, local_rank, cpu_lines)
     if line is not None:
         line["cpu_baseline"] = cpu_line
+        line["bench_wall_s"] = round(time.perf_counter() - T_START, 1)
         print(json.dumps(line), flush=True)
     return 0
 
