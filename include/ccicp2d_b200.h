@@ -203,6 +203,30 @@ int ccicp_register_batch_device_ex(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_se
                                    const double* d_init_Rt, const ccicp_params* params,
                                    ccicp_result* d_out, int32_t* d_corr_idx,
                                    int32_t max_model, int32_t max_scene, int32_t max_cells_hint, void* stream);
+/* ---- the allocation-free variant -----------------------------------------------------------------------------------
+ * NO counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contract and same records as
+ * ccicp_register_batch_device with n_seeds = 1 (device pointers, enqueued on `stream`, 0 = the ctx's), but it calls no
+ * cudaMalloc / cudaFree and no allocating library routine: the scratch memory of the pair kernel (work counters, the
+ * problem list of the exact-order re-run, the kd-tree nodes and rank tables of every CTA's tie replay) is ONE file-scope
+ * device array of CCICP_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until the process exits.
+ * Limits, checked before anything is enqueued (CCICP_E_TOO_LARGE, the reason in ccicp_last_cuda_error):
+ * n_pairs <= CCICP_STATIC_MAX_PAIRS, max_model and max_scene <= CCICP_STATIC_MAX_POINTS, and the pair's working set
+ * must fit one SM's shared memory (the large-scan variant needs a per-CTA workspace of megabytes).  Flags that select
+ * another kernel variant (EXACT_SUMS, TRIM, DIAG_COUNTS, CURV_GATE, BEST_OF_SEEDS, FIRST_BELOW) -> CCICP_E_INVALID.
+ * The launch is capped to the CTAs whose replay scratch fits the array (about 230 for 1081-beam scans, 124 at 2048 points;
+ * the records do not depend on the grid size).  EVERY call on a device shares the array: the counters are cleared on
+ * the stream by each call, and two calls that overlap on the GPU -- different streams or ctxs without an ordering
+ * between them -- race on it.                                                                                      */
+#define CCICP_STATIC_SCRATCH_BYTES (32 << 20)
+#define CCICP_STATIC_MAX_POINTS 2048
+#define CCICP_STATIC_MAX_PAIRS 65536
+int ccicp_register_batch_device_static(ccicp_ctx* ctx, int32_t n_pairs,
+                                       const double* d_model_xy, const int32_t* d_model_off,
+                                       const double* d_scene_xy, const int32_t* d_scene_off,
+                                       const double* d_init_Rt, const ccicp_params* params,
+                                       ccicp_result* d_out, int32_t* d_corr_idx,
+                                       int32_t max_model, int32_t max_scene, void* stream);
 /* ---- scan table: key-frame scans uploaded once, pairs as index lists ---------------------------------------------
  * Loop-closure batches reuse every key-frame scan many times: graph_slam registers each new key frame against its K = 3
  * nearest key frames plus the previous one (graph_slam/include/graph_slam/graphSlamTools.h:26-36,

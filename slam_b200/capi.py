@@ -18,6 +18,7 @@ OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_NOMEM, E_TOO_LARGE, E_ARCH = range(7)
 ST_TOO_FEW_MODEL, ST_TOO_FEW_SCENE, ST_NO_CORR, ST_REFLECTION, ST_DEGENERATE = 1, 2, 4, 8, 16
 ST_TIE_REPLAY, ST_CONVERGED, ST_TREE_OVERFLOW, ST_INFO_SINGULAR, ST_HINT_TOO_SMALL = 32, 64, 128, 256, 512
 ST_NO_SEED_BELOW, ST_EDGE_REJECTED, ST_EXACT_RETRY = 1024, 2048, 4096
+STATIC_SCRATCH_BYTES, STATIC_MAX_POINTS, STATIC_MAX_PAIRS = 32 << 20, 2048, 65536   # ccicp_register_batch_device_static
 F_INFO, F_INFO_FIXED_DY, F_BEST_OF_SEEDS, F_NO_TIE_REPLAY, F_EXACT_SUMS, F_FIRST_BELOW, F_TRIM = 1, 2, 4, 8, 16, 32, 64
 F_DIAG_COUNTS, F_NO_EXACT_RETRY, F_CURV_GATE = 128, 256, 512
 
@@ -48,7 +49,8 @@ SYMBOLS = ["ccicp_abi_version", "ccicp_create", "ccicp_destroy", "ccicp_strerror
            "ccicp_grid_cells", "ccicp_edge_information_lum", "ccicp_knn_candidates", "ccicp_get_diag_counts",
            "ccicp_multi_create", "ccicp_multi_destroy", "ccicp_multi_device_count", "ccicp_multi_ctx", "ccicp_multi_last_error",
            "ccicp_shard_range", "ccicp_register_batch_multi", "ccicp_register_batch_multi_device", "ccicp_multi_sync",
-           "ccicp_multi_gather_kind", "ccicp_scans_upload", "ccicp_register_scan_pairs", "ccicp_scan_features"]
+           "ccicp_multi_gather_kind", "ccicp_scans_upload", "ccicp_register_scan_pairs", "ccicp_scan_features",
+           "ccicp_register_batch_device_static"]
 
 _lib = None
 
@@ -80,6 +82,7 @@ def load():
     lib.ccicp_register_batch.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp]
     lib.ccicp_register_batch_device.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, vp]
     lib.ccicp_register_batch_device_ex.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, i32, vp]
+    lib.ccicp_register_batch_device_static.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(Params), vp, vp, i32, i32, vp]
     lib.ccicp_edge_information_lum.argtypes = [vp, i32, vp, vp, vp, vp, dbl, vp, vp, vp]
     lib.ccicp_knn_candidates.argtypes = [vp, i32, vp, i32, i32, vp]
     lib.ccicp_knn_candidates.restype = i32
@@ -225,6 +228,15 @@ class Context:
         rc = self.lib.ccicp_register_batch_device_ex(self.h, n_pairs, n_seeds, d_model_xy, d_model_off, d_scene_xy,
                                                      d_scene_off, d_init_Rt, C.byref(params), d_out, d_corr or None,
                                                      max_model, max_scene, max_cells_hint, stream or None)
+        self._check(rc)
+
+    def register_batch_device_static(self, n_pairs, d_model_xy, d_model_off, d_scene_xy, d_scene_off, d_init_Rt, params,
+                                     d_out, d_corr, max_model, max_scene, stream=None):
+        """ccicp_register_batch_device_static: the allocation-free device-pointer call (scratch in a fixed device array
+        of STATIC_SCRATCH_BYTES; n_pairs <= STATIC_MAX_PAIRS, scans <= STATIC_MAX_POINTS points)."""
+        rc = self.lib.ccicp_register_batch_device_static(self.h, n_pairs, d_model_xy, d_model_off, d_scene_xy, d_scene_off,
+                                                         d_init_Rt, C.byref(params), d_out, d_corr or None, max_model,
+                                                         max_scene, stream or None)
         self._check(rc)
 
     def sync(self, stream=None):

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <algorithm>
@@ -970,3 +971,123 @@ int ccicp_get_launch_info(ccicp_ctx* ctx, ccicp_launch_info* out) {
 }
 
 }  // extern "C"
+
+// ---- ccicp_register_batch_device_static: the allocation-free variant of ccicp_register_batch_device -------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch memory icp_pair_kernel
+// needs -- its work counters, the list of problems for the exact-order re-run, and the lazily built kd-tree nodes + rank
+// tables of the tie replay of every CTA of the launch -- lives in ONE file-scope device array of
+// CCICP_STATIC_SCRATCH_BYTES, which every GPU that loads the library holds until the process exits.
+//   [0, 256)                              counters {work, re-run work, re-run count} (cleared by every call)
+//   [256, 256 + 4 * CCICP_STATIC_MAX_PAIRS)   problem list of the exact-order re-run (written before it is read)
+//   [.., CCICP_STATIC_SCRATCH_BYTES)      replay_scratch_bytes(max_model) per CTA; the grid is capped to the CTAs that fit
+// Every call shares the array: two calls that overlap on the GPU (different streams, no ordering) race on it.
+static __device__ __align__(256) unsigned char g_static_scratch[CCICP_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+constexpr size_t kStaticListOff = 256;
+constexpr size_t kStaticReplayOff = kStaticListOff + (size_t)CCICP_STATIC_MAX_PAIRS * 4;
+static_assert(kStaticReplayOff % 256 == 0 && kStaticReplayOff < (size_t)CCICP_STATIC_SCRATCH_BYTES, "static scratch layout");
+void* g_static_ptr[kStaticMaxDevices];      // device address of g_static_scratch on each device (the name is a host-side stand-in)
+std::mutex g_static_mu;
+
+int static_fail(ccicp_ctx* ctx, int code, const char* fmt, long long got, long long limit) {
+  char buf[256];
+  snprintf(buf, sizeof(buf), fmt, got, limit);
+  ctx->last_err = std::string("ccicp_register_batch_device_static: ") + buf;
+  return code;
+}
+}  // namespace
+
+extern "C" int ccicp_register_batch_device_static(ccicp_ctx* ctx, int32_t n_pairs, const double* d_model_xy,
+                                                  const int32_t* d_model_off, const double* d_scene_xy,
+                                                  const int32_t* d_scene_off, const double* d_init_Rt,
+                                                  const ccicp_params* params, ccicp_result* d_out, int32_t* d_corr_idx,
+                                                  int32_t max_model, int32_t max_scene, void* stream) {
+  NvtxRange nvtx_("ccicp_register_batch_device_static");
+  if (!ctx || !params || n_pairs < 0 || max_model < 0 || max_scene < 0) return CCICP_E_INVALID;
+  if (n_pairs > 0 && (!d_model_xy || !d_model_off || !d_scene_xy || !d_scene_off || !d_init_Rt || !d_out)) return CCICP_E_INVALID;
+  const uint32_t unsupported = CCICP_F_EXACT_SUMS | CCICP_F_TRIM | CCICP_F_DIAG_COUNTS | CCICP_F_CURV_GATE | CCICP_F_BEST_OF_SEEDS | CCICP_F_FIRST_BELOW;
+  if (params->flags & unsupported)
+    return static_fail(ctx, CCICP_E_INVALID, "flags 0x%llx select a kernel variant this entry point does not offer (unsupported mask 0x%llx)",
+                       (long long)params->flags, (long long)unsupported);
+  if (n_pairs > CCICP_STATIC_MAX_PAIRS)
+    return static_fail(ctx, CCICP_E_TOO_LARGE, "n_pairs %lld exceeds CCICP_STATIC_MAX_PAIRS %lld", n_pairs, CCICP_STATIC_MAX_PAIRS);
+  if (max_model > CCICP_STATIC_MAX_POINTS)
+    return static_fail(ctx, CCICP_E_TOO_LARGE, "max_model %lld exceeds CCICP_STATIC_MAX_POINTS %lld", max_model, CCICP_STATIC_MAX_POINTS);
+  if (max_scene > CCICP_STATIC_MAX_POINTS)
+    return static_fail(ctx, CCICP_E_TOO_LARGE, "max_scene %lld exceeds CCICP_STATIC_MAX_POINTS %lld", max_scene, CCICP_STATIC_MAX_POINTS);
+  if (ctx->device < 0 || ctx->device >= kStaticMaxDevices) return CCICP_E_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  if (n_pairs == 0) return CCICP_OK;
+
+  // set-up, once per device, with that device current: the DEVICE address of the array
+  unsigned char* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[ctx->device]) {
+      void* p = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+      if (e != cudaSuccess || !p) return fail_cuda(ctx, e != cudaSuccess ? e : cudaErrorInvalidSymbol, "cudaGetSymbolAddress(g_static_scratch)");
+      g_static_ptr[ctx->device] = p;
+    }
+    base = (unsigned char*)g_static_ptr[ctx->device];
+  }
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+
+  IcpArgs a{};
+  a.mcap = round_up(max_model < 32 ? 32 : max_model, 32);
+  a.scap = round_up(max_scene < 32 ? 32 : max_scene, 32);
+  a.ccap = max_cells_for(max_model);
+  if (a.ccap < 64) a.ccap = 64;
+  const bool retry = !(params->flags & CCICP_F_NO_EXACT_RETRY);
+  cudaFuncAttributes fa_on, fa_ex;
+  CK(cudaFuncGetAttributes(&fa_on, icp_pair_kernel));
+  CK(cudaFuncGetAttributes(&fa_ex, icp_pair_exact_kernel));
+  size_t static_smem = fa_on.sharedSizeBytes;
+  if (retry && fa_ex.sharedSizeBytes > static_smem) static_smem = fa_ex.sharedSizeBytes;
+  const size_t smem = workset_bytes(a.mcap, a.scap, a.ccap, false);
+  if (smem + static_smem > (size_t)ctx->max_smem_optin)       // the L2 variant needs a per-CTA workspace of megabytes: not offered here
+    return static_fail(ctx, CCICP_E_TOO_LARGE, "the pair's working set (%lld bytes) exceeds one SM's shared memory (%lld); use ccicp_register_batch_device",
+                       (long long)(smem + static_smem), ctx->max_smem_optin);
+  int occ = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, icp_pair_kernel, kThreadsOnChip, smem));
+  if (occ < 1) return CCICP_E_TOO_LARGE;
+  const size_t per_cta = replay_scratch_bytes(max_model);
+  const long long fit = (long long)(((size_t)CCICP_STATIC_SCRATCH_BYTES - kStaticReplayOff) / per_cta);
+  long long grid = (long long)occ * ctx->sm_count;
+  if (grid > fit) grid = fit;
+  if (grid > n_pairs) grid = n_pairs;
+  if (grid < 1) return CCICP_E_TOO_LARGE;
+
+  int32_t* cnt = (int32_t*)base;
+  a.model_xy = d_model_xy; a.model_off = d_model_off; a.scene_xy = d_scene_xy; a.scene_off = d_scene_off;
+  a.init_Rt = d_init_Rt; a.out = d_out; a.corr_idx = d_corr_idx;
+  a.work_counter = cnt;
+  a.scratch = (char*)base + kStaticReplayOff; a.scratch_per_cta = per_cta;
+  a.pair_base = 0; a.n_pairs = n_pairs; a.n_seeds = 1; a.seeds_per_item = 1; a.items_per_pair = 1;
+  a.max_iter = params->max_iter; a.flags = params->flags; a.min_delta = params->min_delta; a.indist = params->indist;
+  a.trim_frac = params->trim_frac;
+  a.curv_tol = params->curv_tol; a.feat_radius = params->feat_radius; a.feat_k = params->feat_k;
+  a.total_scene = 0; a.max_model = max_model;
+
+  CK(cudaMemsetAsync(cnt, 0, 256, st));       // the array keeps the last call's contents: the counters must start at zero
+  icp_pair_kernel<<<(unsigned)grid, kThreadsOnChip, smem, st>>>(a);
+  CK(cudaGetLastError());
+  if (retry) {
+    int32_t* list = (int32_t*)(base + kStaticListOff);
+    collect_retry_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, st>>>(d_out, 0, (int)n_pairs, list, cnt + 2);
+    CK(cudaGetLastError());
+    IcpArgs a2 = a;
+    a2.item_list = list; a2.item_count = cnt + 2; a2.work_counter = cnt + 1;
+    int occ2 = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, icp_pair_exact_kernel, kThreadsOnChip, smem));
+    if (occ2 < 1) return CCICP_E_TOO_LARGE;
+    long long grid2 = (long long)occ2 * ctx->sm_count;
+    if (grid2 > grid) grid2 = grid;              // the replay scratch holds `grid` CTAs
+    icp_pair_exact_kernel<<<(unsigned)grid2, kThreadsOnChip, smem, st>>>(a2);
+    CK(cudaGetLastError());
+  }
+  return CCICP_OK;
+}
