@@ -9,6 +9,7 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $o
 nproc > $out/nproc.txt
 profiles/fp32_peak > $out/fp32_unfused_peak.json 2> $out/fp32.err
 if [ "$2" != "skip-tests" ]; then
+  timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -p no:cacheprovider > $out/pytest_no_alloc_alone.log 2>&1; echo "pytest rc=$?" >> $out/pytest_no_alloc_alone.log
   timeout 1500 python -m pytest tests -m gpu -q -p no:cacheprovider > $out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $out/pytest_gpu.log
   timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; echo "smoke rc=$?" >> $out/smoke.log
 fi
@@ -29,4 +30,4 @@ if [ $rc -eq 0 ]; then
     ncu -i $out/large_full.ncu-rep --page raw --csv > $out/large_full_raw.csv 2>/dev/null
   fi
 fi
-tail -3 $out/pytest_gpu.log 2>/dev/null; tail -2 $out/smoke.log 2>/dev/null; cat $out/bench_1gpu.json; tail -2 $out/bench_1gpu.err; cat $out/bench_ref.json
+tail -3 $out/pytest_no_alloc_alone.log 2>/dev/null; tail -3 $out/pytest_gpu.log 2>/dev/null; tail -2 $out/smoke.log 2>/dev/null; cat $out/bench_1gpu.json; tail -2 $out/bench_1gpu.err; cat $out/bench_ref.json
