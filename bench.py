@@ -357,7 +357,8 @@ def sub_config(torch, dev, ctx, capi, name, workload, batch, init_Rt, n_seeds, p
     barrier = torch.cuda.synchronize
     dev_ms, k_ms, li, e2e_ms, e2e_l = time_legs(torch, ctx, db, stream, steps, warmup, barrier)
     units = db.n_pairs * n_seeds
-    kernel = {0: "icp_pair_kernel", 1: "icp_pair_l2_kernel", 4: "icp_pair_cluster_kernel"}.get(int(li.kernel_variant), kernel)
+    kernel = {0: "icp_pair_seeds_kernel" if n_seeds > 1 else "icp_pair_kernel", 1: "icp_pair_l2_kernel",
+              4: "icp_pair_cluster_kernel"}.get(int(li.kernel_variant), kernel)
     dram, _, cap = kernel_traffic(traffic, kernel, db.n_pairs)
     ach = db.alg_bytes / (k_ms * 1e-3) / 1e9
     rec = {"workload": workload, "value": units / (dev_ms * 1e-3), "unit": unit_name, "ms_per_step": dev_ms, "kernel_ms": k_ms,
@@ -487,7 +488,7 @@ def gpu_arm(args, rank, world, local_rank, cpu_lines):
         configs["c5"], n5 = sub_config(
             torch, dev, ctx, capi, "c5", "C5: %d pairs x %d initial pose seeds (seed 0 = identity, the rest uniform in +-10 m, 0..2 pi), %d fixed "
             "iterations each, best seed selected on device" % (b5.n_pairs, C5_SEEDS, ITERS),
-            b5, init5, C5_SEEDS, prm5, args.sub_steps, 2, "icp_pair_kernel", "problems/s", traffic, peak, peak_src, cpu_lines.get("c5"))
+            b5, init5, C5_SEEDS, prm5, args.sub_steps, 2, "icp_pair_seeds_kernel", "problems/s", traffic, peak, peak_src, cpu_lines.get("c5"))
         configs["c5"]["pairs_per_s"] = configs["c5"]["value"] / C5_SEEDS
         extra_launches += n4 + n5
 

@@ -189,7 +189,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   if (curv && (exact || trim || diag || !(prm->curv_tol >= 0.0) || !(prm->feat_radius > 0.0) || prm->feat_k < 1)) return CCICP_E_INVALID;
   if (trim && (exact || !(prm->trim_frac > 0.0) || prm->trim_frac > 1.0)) return CCICP_E_INVALID;
   if (diag && (exact || trim)) return CCICP_E_INVALID;
-  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : diag ? icp_pair_diag_kernel : curv ? icp_pair_curv_kernel : icp_pair_kernel;
+  auto k_on = exact ? icp_pair_exact_kernel : trim ? icp_pair_trim_kernel : diag ? icp_pair_diag_kernel : curv ? icp_pair_curv_kernel : n_seeds > 1 ? icp_pair_seeds_kernel : icp_pair_kernel;
   auto k_l2 = exact ? icp_pair_l2_exact_kernel : trim ? icp_pair_l2_trim_kernel : diag ? icp_pair_l2_diag_kernel : curv ? icp_pair_l2_curv_kernel : icp_pair_l2_kernel;
   cudaFuncAttributes fa_on;
   CK(cudaFuncGetAttributes(&fa_on, k_on));
@@ -413,7 +413,7 @@ int ccicp_create(ccicp_ctx** out, int device) {
   ok = ok && allow_max_smem(icp_pair_kernel, mo) && allow_max_smem(icp_pair_l2_kernel, mo) && allow_max_smem(icp_pair_exact_kernel, mo) &&
        allow_max_smem(icp_pair_l2_exact_kernel, mo) && allow_max_smem(icp_pair_trim_kernel, mo) && allow_max_smem(icp_pair_l2_trim_kernel, mo) &&
        allow_max_smem(icp_pair_diag_kernel, mo) && allow_max_smem(icp_pair_l2_diag_kernel, mo) && allow_max_smem(icp_pair_curv_kernel, mo) &&
-       allow_max_smem(icp_pair_l2_curv_kernel, mo) && allow_max_smem(icp_pair_cluster_kernel, mo);
+       allow_max_smem(icp_pair_l2_curv_kernel, mo) && allow_max_smem(icp_pair_cluster_kernel, mo) && allow_max_smem(icp_pair_seeds_kernel, mo);
   if (!ok) { delete ctx; cudaGetLastError(); return CCICP_E_CUDA; }
   *out = ctx;
   return CCICP_OK;

@@ -272,7 +272,7 @@ __device__ __noinline__ void trim_select(const IcpArgs& a, Smem& s, int ns, int 
   }
 }
 
-template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false, bool kDiag = false, bool kCurv = false>
+template <int kThreads, bool kGlobal, bool kExact, bool kTrim = false, bool kDiag = false, bool kCurv = false, int kLoops = CCICP_ROW_LOOPS>
 __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
   constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(16) char smem_raw[];
@@ -403,7 +403,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               if constexpr (kTrim) { if (start == kNoSlot) start = trim_keys[i] & 0xFFFFu; }
               if constexpr (kCurv) {
                 const float qc = scurv[i];
-                nn_search<kGlobal, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
+                nn_search<kGlobal, false, true, kLoops>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
                 if (tie) {     // several compatible model points at the float minimum (rare): the lowest model index wins
                   const QPack q2 = pack_query(qx, qy);
                   int bo = 0x7fffffff;
@@ -412,7 +412,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
                   tie = 0;
                 }
               } else {
-                nn_search<kGlobal, kDiag>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
+                nn_search<kGlobal, kDiag, false, kLoops>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals);
               }
               if (kDiag) diag_queries++;
               if (bslot >= 0 && (double)best < a.indist) {
@@ -568,7 +568,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               float best; int bslot, tie;
               if constexpr (kCurv) {
                 const float qc = scurv[i];
-                nn_search<kGlobal, false, true>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals, mcurv, qc, ctol);
+                nn_search<kGlobal, false, true, kLoops>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals, mcurv, qc, ctol);
                 if (tie) {
                   const QPack q2 = pack_query(qx, qy);
                   int bo = 0x7fffffff;
@@ -576,7 +576,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
                     if (!(fabsf(mcurv[j] - qc) > ctol) && dist2(s.mpts[j], q2) == best && (int)s.morig[j] < bo) { bo = s.morig[j]; bslot = j; }
                 }
               } else {
-                nn_search<kGlobal, false>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
+                nn_search<kGlobal, false, false, kLoops>(s.mpts, s.cstart, g, qx, qy, gate_f, kNoSlot, best, bslot, tie, diag_evals);
               }
               if (bslot >= 0 && (double)best < a.indist) slot = (unsigned)bslot;
               if constexpr (kTrim) trim_keys[i] = slot != kNoSlot ? __float_as_uint(best) : 0xFFFFFFFFu;
@@ -661,6 +661,11 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
 
 __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_kernel(const IcpArgs a) {
   icp_pair_body<kThreadsOnChip, false, false>(a);
+}
+
+// Multi-seed launches (config C5: far hypotheses, cold starts): the candidate loop of long rows (nn_grid.h, kLoops = 1).
+__global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_seeds_kernel(const IcpArgs a) {
+  icp_pair_body<kThreadsOnChip, false, false, false, false, false, 1>(a);
 }
 
 // Large scans (config C4): same algorithm, working set in the CTA's global workspace (L2/L1 resident).

@@ -57,8 +57,8 @@ template <class T> inline T max(T a, T b) { return a > b ? a : b; }
 #define CCICP_CAND_UNROLL 2
 #endif
 #ifndef CCICP_ROW_LOOPS
-#define CCICP_ROW_LOOPS 1
-#endif
+#define CCICP_ROW_LOOPS 4   // on-chip candidate loop: 4 = one loop over unmasked 4-slot chunks (shipped), 1 = one plain loop per row,
+#endif                     // 0 = flat loop over the three ranges (the L2 variant always uses that one)
 #ifndef CCICP_ROW_UNROLL
 #define CCICP_ROW_UNROLL 4
 #endif
@@ -70,6 +70,10 @@ namespace ccicp {
 
 constexpr int kCandUnroll = CCICP_CAND_UNROLL;              // candidate loop of nn_search
 constexpr int kRowUnroll = CCICP_ROW_UNROLL;
+#ifndef CCICP_ROW_CHUNK
+#define CCICP_ROW_CHUNK 4
+#endif
+constexpr int kRowChunk = CCICP_ROW_CHUNK;                 // CCICP_ROW_LOOPS == 4: slots per chunk (2: 3.33 ms, 3: 3.13 ms, 4: 3.00 ms on C2)
 constexpr int kCandUnrollDense = CCICP_CAND_UNROLL_DENSE;   // L2 variant: the candidates come from global memory, more loads in flight
 constexpr unsigned kNoSlot = 0xFFFFu;
 
@@ -163,7 +167,7 @@ NN_D int floor_int(float x) {      // (int)floorf(x) as one conversion
 // kDiag: count the distance evaluations into `evals` (diagnostics instantiation only).
 // kCurv (CCICP_F_CURV_GATE, an extra without reference counterpart): a candidate whose curvature mcurv[j] differs from
 // the query's `qc` by more than `ctol` is not a candidate at all (NaN = no feature: compatible with everything).
-template <bool kDense, bool kDiag = false, bool kCurv = false>
+template <bool kDense, bool kDiag = false, bool kCurv = false, int kLoops = CCICP_ROW_LOOPS>
 NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, float qx, float qy, float gate_f,
                     unsigned warm, float& best, int& bslot, int& tie, int& evals, const float* mcurv = nullptr,
                     float qc = 0.0f, float ctol = 0.0f) {
@@ -176,6 +180,7 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
   const float uy = fminf(fmaxf(__fmul_rn(__fsub_rn(qy, g.miny), inv_h), -1.0e6f), 1.0e6f);
   const float slop = 0.01f + 4e-7f * fmaxf(fabsf(ux), fabsf(uy));
   const QPack q2 = pack_query(qx, qy);
+  const int cend = kLoops == 4 ? (int)cs[G * G] : 0;      // one past the class's last slot
   // Without a warm start an upper bound B is probed first: the home cell, then blocks of radius 1, 2, 4, ... cells
   // (r < 0 below), until a block holds a point or the gate radius is covered.  The final pass (r = -1) is the exact
   // sweep of every cell that can hold a point with dis <= min(B+, gate).  The column span of a chunk of rows is cut
@@ -203,6 +208,7 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
       ya = floor_int(uy - su); yb = floor_int(uy + su);
     }
     xa = max(xa, 0); xb = min(xb, G - 1); ya = max(ya, 0); yb = min(yb, G - 1);
+    int cov = 0;      // kLoops == 4: one past the last slot this pass has evaluated
     if (xa <= xb) {
       const bool wide = kDense && r < 0 && yb - ya >= 3;
       for (int y = ya; y <= yb; y += 3) {
@@ -234,7 +240,53 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
         // On chip: one plain loop per row -- no index mapping (13 instead of 18.5 instructions per candidate) but three
         // trip counts per warp (+22 % trips): +3.5 % on C2.  The L2 variant keeps the flat loop over the three ranges (all
         // lanes of a warp run the same number of trips, more loads in flight): row loops cost it 13 %.
-        if (CCICP_ROW_LOOPS && !kDense) {
+        if (kLoops == 4 && !kDense) {
+          // ONE loop over chunks of kRowChunk slots covering the three rows.  A chunk that runs past the end of its row
+          // evaluates the slots that follow: points of the SAME class outside the box, which provably cannot win or tie
+          // (every point with dis <= bound lies inside the box), so nothing is masked -- except in the last slots of the
+          // class, where the chunk would reach the other class / the end of the array (cold path, masked).
+          // Rows ascend in slot order, so the slots a chunk evaluates past its row's end may be the first slots of the
+          // next row (a vertical wall: nothing between them): `cov` = end of the slots already evaluated in this pass;
+          // a row starts there at the earliest, so no point is evaluated twice (a duplicate of the best would read as a tie).
+          const int s0 = max(j0, cov), c0 = (max(e0 - s0, 0) + kRowChunk - 1) / kRowChunk;
+          cov = c0 ? s0 + c0 * kRowChunk : cov;
+          const int s1 = max(j1, cov), c1 = (max(e1 - s1, 0) + kRowChunk - 1) / kRowChunk;
+          cov = c1 ? s1 + c1 * kRowChunk : cov;
+          const int s2 = max(j2, cov), c2 = (max(e2 - s2, 0) + kRowChunk - 1) / kRowChunk;
+          cov = c2 ? s2 + c2 * kRowChunk : cov;
+          const int c01 = c0 + c1, nchunk = c01 + c2;
+          const int vb1 = s1 - c0 * kRowChunk, vb2 = s2 - c01 * kRowChunk;
+#pragma unroll 1
+          for (int t = 0; t < nchunk; t++) {
+            int vb = t >= c0 ? vb1 : s0;
+            vb = t >= c01 ? vb2 : vb;
+            const int j = vb + t * kRowChunk;
+            float d[kRowChunk];
+            if (j + kRowChunk <= cend) {
+#pragma unroll
+              for (int c = 0; c < kRowChunk; c++) {
+                d[c] = dist2(mpts[j + c], q2);
+                if (kCurv) d[c] = fabsf(mcurv[j + c] - qc) > ctol ? CUDART_INF_F : d[c];
+              }
+            } else {
+#pragma unroll
+              for (int c = 0; c < kRowChunk; c++) {
+                const int jc = min(j + c, cend - 1);
+                d[c] = dist2(mpts[jc], q2);
+                if (kCurv) d[c] = fabsf(mcurv[jc] - qc) > ctol ? CUDART_INF_F : d[c];
+                d[c] = j + c < cend ? d[c] : CUDART_INF_F;
+              }
+            }
+#pragma unroll
+            for (int c = 0; c < kRowChunk; c++) {
+              bslot = d[c] < best ? j + c : bslot;
+              second = fminf(second, fmaxf(d[c], best));
+              best = fminf(best, d[c]);
+            }
+          }
+        } else if (kLoops && !kDense) {
+          // (kLoops == 1: the instantiation of multi-seed launches -- cold queries and far seeds sweep long rows, where a
+          // plain unrolled loop per row is cheaper than the chunk bookkeeping: C5 867 k against 837 k problems/s)
           const int jb[3] = {j0, j1, j2}, je[3] = {e0, e1, e2};
 #pragma unroll
           for (int k = 0; k < 3; k++) {
