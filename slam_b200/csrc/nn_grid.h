@@ -70,9 +70,16 @@ namespace ccicp {
 
 constexpr int kCandUnroll = CCICP_CAND_UNROLL;              // candidate loop of nn_search
 constexpr int kRowUnroll = CCICP_ROW_UNROLL;
+#ifndef CCICP_DENSE_CHUNKS
+#define CCICP_DENSE_CHUNKS 1
+#endif
+#ifndef CCICP_ROW_CHUNK_DENSE
+#define CCICP_ROW_CHUNK_DENSE 8
+#endif
 #ifndef CCICP_ROW_CHUNK
 #define CCICP_ROW_CHUNK 4
 #endif
+constexpr int kRowChunkDense = CCICP_ROW_CHUNK_DENSE;     // L2 variant (one C4 wave: flat loop 16.6 ms, chunks of 4: 15.0, of 8: 14.2)
 constexpr int kRowChunk = CCICP_ROW_CHUNK;                 // CCICP_ROW_LOOPS == 4: slots per chunk (2: 3.33 ms, 3: 3.13 ms, 4: 3.00 ms on C2)
 constexpr int kCandUnrollDense = CCICP_CAND_UNROLL_DENSE;   // L2 variant: the candidates come from global memory, more loads in flight
 constexpr unsigned kNoSlot = 0xFFFFu;
@@ -237,40 +244,41 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
         const int n0 = e0 - j0, n01 = n0 + (e1 - j1), tot = n01 + (e2 - j2);
         const int o1 = j1 - n0, o2 = j2 - n01;
         if (kDiag) evals += tot;
-        // On chip: one plain loop per row -- no index mapping (13 instead of 18.5 instructions per candidate) but three
-        // trip counts per warp (+22 % trips): +3.5 % on C2.  The L2 variant keeps the flat loop over the three ranges (all
-        // lanes of a warp run the same number of trips, more loads in flight): row loops cost it 13 %.
-        if (kLoops == 4 && !kDense) {
-          // ONE loop over chunks of kRowChunk slots covering the three rows.  A chunk that runs past the end of its row
+        // History of this loop: a flat loop over the three ranges (18.5 instructions per candidate: the range of a candidate
+        // is picked per candidate), then on chip one plain unrolled loop per row (13 per candidate, but three trip counts per
+        // warp and a remainder path that a 3.6-candidate row rarely leaves), now chunks (below) in both variants.
+        if (kLoops == 4 && (!kDense || CCICP_DENSE_CHUNKS)) {
+          constexpr int kCh = kDense ? kRowChunkDense : kRowChunk;
+          // ONE loop over chunks of kCh slots covering the three rows.  A chunk that runs past the end of its row
           // evaluates the slots that follow: points of the SAME class outside the box, which provably cannot win or tie
           // (every point with dis <= bound lies inside the box), so nothing is masked -- except in the last slots of the
           // class, where the chunk would reach the other class / the end of the array (cold path, masked).
           // Rows ascend in slot order, so the slots a chunk evaluates past its row's end may be the first slots of the
           // next row (a vertical wall: nothing between them): `cov` = end of the slots already evaluated in this pass;
           // a row starts there at the earliest, so no point is evaluated twice (a duplicate of the best would read as a tie).
-          const int s0 = max(j0, cov), c0 = (max(e0 - s0, 0) + kRowChunk - 1) / kRowChunk;
-          cov = c0 ? s0 + c0 * kRowChunk : cov;
-          const int s1 = max(j1, cov), c1 = (max(e1 - s1, 0) + kRowChunk - 1) / kRowChunk;
-          cov = c1 ? s1 + c1 * kRowChunk : cov;
-          const int s2 = max(j2, cov), c2 = (max(e2 - s2, 0) + kRowChunk - 1) / kRowChunk;
-          cov = c2 ? s2 + c2 * kRowChunk : cov;
+          const int s0 = max(j0, cov), c0 = (max(e0 - s0, 0) + kCh - 1) / kCh;
+          cov = c0 ? s0 + c0 * kCh : cov;
+          const int s1 = max(j1, cov), c1 = (max(e1 - s1, 0) + kCh - 1) / kCh;
+          cov = c1 ? s1 + c1 * kCh : cov;
+          const int s2 = max(j2, cov), c2 = (max(e2 - s2, 0) + kCh - 1) / kCh;
+          cov = c2 ? s2 + c2 * kCh : cov;
           const int c01 = c0 + c1, nchunk = c01 + c2;
-          const int vb1 = s1 - c0 * kRowChunk, vb2 = s2 - c01 * kRowChunk;
+          const int vb1 = s1 - c0 * kCh, vb2 = s2 - c01 * kCh;
 #pragma unroll 1
           for (int t = 0; t < nchunk; t++) {
             int vb = t >= c0 ? vb1 : s0;
             vb = t >= c01 ? vb2 : vb;
-            const int j = vb + t * kRowChunk;
-            float d[kRowChunk];
-            if (j + kRowChunk <= cend) {
+            const int j = vb + t * kCh;
+            float d[kCh];
+            if (j + kCh <= cend) {
 #pragma unroll
-              for (int c = 0; c < kRowChunk; c++) {
+              for (int c = 0; c < kCh; c++) {
                 d[c] = dist2(mpts[j + c], q2);
                 if (kCurv) d[c] = fabsf(mcurv[j + c] - qc) > ctol ? CUDART_INF_F : d[c];
               }
             } else {
 #pragma unroll
-              for (int c = 0; c < kRowChunk; c++) {
+              for (int c = 0; c < kCh; c++) {
                 const int jc = min(j + c, cend - 1);
                 d[c] = dist2(mpts[jc], q2);
                 if (kCurv) d[c] = fabsf(mcurv[jc] - qc) > ctol ? CUDART_INF_F : d[c];
@@ -278,7 +286,7 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
               }
             }
 #pragma unroll
-            for (int c = 0; c < kRowChunk; c++) {
+            for (int c = 0; c < kCh; c++) {
               bslot = d[c] < best ? j + c : bslot;
               second = fminf(second, fmaxf(d[c], best));
               best = fminf(best, d[c]);
