@@ -30,7 +30,10 @@ namespace ccicp {
 //   on-chip : 256 threads, the pair's working set in dynamic shared memory (scans up to ~6000 points per cloud)
 //   L2      : 1024 threads (64 registers), one CTA per SM, the working set in a per-CTA global workspace that stays L2/L1-resident
 //             (scans up to CCICP_MAX_POINTS; config C4 = 32768 points per cloud)
-constexpr int kThreadsOnChip = 256;
+#ifndef CCICP_THREADS_ONCHIP
+#define CCICP_THREADS_ONCHIP 256
+#endif
+constexpr int kThreadsOnChip = CCICP_THREADS_ONCHIP;
 #ifndef CCICP_L2_THREADS
 #define CCICP_L2_THREADS 1024
 #endif

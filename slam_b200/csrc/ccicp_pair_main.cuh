@@ -663,9 +663,12 @@ __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_ker
   icp_pair_body<kThreadsOnChip, false, false>(a);
 }
 
+#ifndef CCICP_SEEDS_LOOPS
+#define CCICP_SEEDS_LOOPS 1
+#endif
 // Multi-seed launches (config C5: far hypotheses, cold starts): the candidate loop of long rows (nn_grid.h, kLoops = 1).
 __global__ void __launch_bounds__(kThreadsOnChip, CCICP_MIN_BLOCKS) icp_pair_seeds_kernel(const IcpArgs a) {
-  icp_pair_body<kThreadsOnChip, false, false, false, false, false, 1>(a);
+  icp_pair_body<kThreadsOnChip, false, false, false, false, false, CCICP_SEEDS_LOOPS>(a);
 }
 
 // Large scans (config C4): same algorithm, working set in the CTA's global workspace (L2/L1 resident).
