@@ -148,7 +148,7 @@ NN_D float dist2(const float2 p, const QPack& q) {
 NN_D float sqrt_up(float x) {
 #if defined(__CUDA_ARCH__)
   float r;
-  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));   // ftz: a subnormal bound reads as 0, the slop term (>= 0.01 cell) covers it
   return r;
 #else
   return __fsqrt_ru(x);
@@ -208,7 +208,7 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
       xa = cx - r; xb = cx + r; ya = cy - r; yb = cy + r;
     } else {
       // keep only the bound: restart from the next float above B so every point is tested exactly once
-      best = __int_as_float(__float_as_int(best) + (best < CUDART_INF_F ? 1 : 0));
+      best = __int_as_float((int)min((unsigned)__float_as_int(best) + 1u, 0x7f800000u));   // next float above B, +inf stays
       second = CUDART_INF_F; bslot = -1;
       su = sqrt_up(fminf(best, gate_f)) * inv_h * 1.00001f + slop;   // search radius in cells, rounded up
       xa = floor_int(ux - su); xb = floor_int(ux + su);
