@@ -222,7 +222,14 @@ def load_traffic():
         t = json.load(open(p))
     except Exception:
         return None
-    t["stale"] = t.get("lib_sha256") != lib_sha256()
+    # same binary, or (nvcc builds are not bit-reproducible) a rebuild from the same sources and flags
+    from slam_b200.build import source_sha256
+    if t.get("lib_sha256") == lib_sha256():
+        t["stale"], t["match"] = False, "library"
+    elif t.get("src_sha256") and t.get("src_sha256") == source_sha256():
+        t["stale"], t["match"] = False, "sources"
+    else:
+        t["stale"], t["match"] = True, None
     return t
 
 
@@ -242,7 +249,7 @@ def issue_roofline(traffic, kernel, units, k_ms, sms, clocks):
     It says how busy the schedulers are, NOT how much of the work is needed (see roofline_useful)."""
     if traffic and traffic.get("stale"):
         return {"bound": "issue", "frac": None, "stale": True,
-                "why": "profiles/traffic.json was captured from another build of the library (lib_sha256 differs)"}
+                "why": "profiles/traffic.json was captured from a library built from other sources (lib_sha256 and src_sha256 differ)"}
     _, instr, cap = kernel_traffic(traffic, kernel, units)
     if not instr:
         return None
@@ -531,7 +538,7 @@ def gpu_arm(args, rank, world, local_rank, cpu_lines):
                                 "note": "per ICP launch: icp_pair_kernel + collect_retry_kernel + the exact-order re-run kernel (usually empty)"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": dram, "kernel": "icp_pair_kernel", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
-                     "peak_source": peak_src, "traffic_stale": bool(traffic and traffic.get("stale")),
+                     "peak_source": peak_src, "traffic_stale": bool(traffic and traffic.get("stale")), "traffic_match": (traffic or {}).get("match"),
                      "note": "contract field.  The kernel keeps a pair on chip and moves only the algorithmic bytes, so HBM is not what "
                              "binds it (SURVEY.md 8(d)): roofline_useful is the fraction the >= 60 % target is about, roofline_issue the "
                              "scheduler occupancy"},

@@ -40,6 +40,9 @@ try:
 except Exception:
     t = {}
 t["lib_sha256"] = sha
+sys.path.insert(0, root)
+from slam_b200.build import source_sha256
+t["src_sha256"] = source_sha256()      # sources + flags in the tree now: run this right after the capture, before editing them
 try: t["commit"] = subprocess.run(["git", "-C", root, "rev-parse", "--short", "HEAD"], stdout=subprocess.PIPE, text=True).stdout.strip()
 except Exception: pass
 t.setdefault("kernels", {})[kname] = k

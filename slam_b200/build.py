@@ -45,6 +45,21 @@ def _run(cmd, verbose):
     return r.stdout
 
 
+def source_sha256():
+    """SHA-256 over the CUDA sources of the product library and its compiler flags.  nvcc does not produce bit-identical
+    libraries from identical sources (two builds in a row differ), so profiles/traffic.json is stamped with this as well
+    as with the SHA-256 of the binary the captures were taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    files = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".h"))]
+    files.append(os.path.join(ROOT, "include", "ccicp2d_b200.h"))
+    for f in files:
+        h.update(os.path.basename(f).encode() + b"\0")
+        h.update(open(f, "rb").read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
 def nvcc_path():
     p = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(p):
