@@ -111,7 +111,7 @@ def build_host_tests(force=False, verbose=False):
     out2 = os.path.join(d, "libnn_grid_host.so")
     srcs2 = [os.path.join(d, "nn_grid_host.cpp"), os.path.join(CSRC, "nn_grid.h")]
     if force or _newer(out2, srcs2):
-        _run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", out2, srcs2[0]], verbose)
+        _run(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", out2, srcs2[0]], verbose)
     return out
 
 

@@ -70,6 +70,12 @@ namespace ccicp {
 
 constexpr int kCandUnroll = CCICP_CAND_UNROLL;              // candidate loop of nn_search
 constexpr int kRowUnroll = CCICP_ROW_UNROLL;
+#ifndef CCICP_CHUNK_MIN2
+#define CCICP_CHUNK_MIN2 0         // on chip (4-slot chunks): the deferred slot look-up costs more than the tournament saves (3.03 against 2.95 ms)
+#endif
+#ifndef CCICP_CHUNK_MIN2_DENSE
+#define CCICP_CHUNK_MIN2_DENSE 1   // large-scan variants (8-slot chunks): 13.9 against 14.2 ms per C4 wave
+#endif
 #ifndef CCICP_DENSE_CHUNKS
 #define CCICP_DENSE_CHUNKS 1
 #endif
@@ -162,6 +168,42 @@ NN_D int floor_int(float x) {      // (int)floorf(x) as one conversion
 #endif
 }
 
+// ---- pieces of the chunked candidate loop ----------------------------------------------------------------------------
+// distances of the kCh slots from j on; slots past the class's last one (cend) read the last point and count as +inf
+template <int kCh, bool kCurv>
+NN_D void chunk_dists(const float2* mpts, const float* mcurv, int j, int cend, const QPack& q2, float qc, float ctol,
+                      float (&d)[kCh]) {
+  if (j + kCh <= cend) {
+#pragma unroll
+    for (int c = 0; c < kCh; c++) {
+      d[c] = dist2(mpts[j + c], q2);
+      if (kCurv) d[c] = fabsf(mcurv[j + c] - qc) > ctol ? CUDART_INF_F : d[c];
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < kCh; c++) {
+      const int jc = min(j + c, cend - 1);
+      d[c] = dist2(mpts[jc], q2);
+      if (kCurv) d[c] = fabsf(mcurv[jc] - qc) > ctol ? CUDART_INF_F : d[c];
+      d[c] = j + c < cend ? d[c] : CUDART_INF_F;
+    }
+  }
+}
+// the two smallest of d[B .. B+N) (with multiplicity: lo == s iff the minimum is attained twice), by a min/max tournament:
+// 7 instructions for four values and 17 for eight, where tracking (best, second, slot) per candidate costs 5 each
+template <int B, int N, int kCh>
+NN_D void two_smallest(const float (&d)[kCh], float& lo, float& s) {
+  if constexpr (N == 1) { lo = d[B]; s = CUDART_INF_F; }
+  else if constexpr (N == 2) { lo = fminf(d[B], d[B + 1]); s = fmaxf(d[B], d[B + 1]); }
+  else {
+    float la, sa, lb, sb;
+    two_smallest<B, N / 2, kCh>(d, la, sa);
+    two_smallest<B + N / 2, N - N / 2, kCh>(d, lb, sb);
+    lo = fminf(la, lb);
+    s = fminf(fmaxf(la, lb), fminf(sa, sb));
+  }
+}
+
 // ---- exact float nearest neighbour over one class grid: row sweep -------------------------------------------------
 // Row sweep in chunks of three grid rows.  An upper bound `best` comes from the previous iteration's match (warm
 // start) or, failing that, from probing the home cell and then the 3x3 block.  A row is cut to the cell span that can
@@ -179,6 +221,7 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
                     unsigned warm, float& best, int& bslot, int& tie, int& evals, const float* mcurv = nullptr,
                     float qc = 0.0f, float ctol = 0.0f) {
   best = CUDART_INF_F; bslot = -1;
+  int jbest = -1;                   // two-smallest mode: first slot of the chunk that holds the minimum
   float second = CUDART_INF_F;      // second smallest distance seen (with multiplicity): tie <=> second == best
   const int G = g.G;
   const float inv_h = g.inv_h;
@@ -209,7 +252,7 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
     } else {
       // keep only the bound: restart from the next float above B so every point is tested exactly once
       best = __int_as_float((int)min((unsigned)__float_as_int(best) + 1u, 0x7f800000u));   // next float above B, +inf stays
-      second = CUDART_INF_F; bslot = -1;
+      second = CUDART_INF_F; bslot = -1; jbest = -1;
       su = sqrt_up(fminf(best, gate_f)) * inv_h * 1.00001f + slop;   // search radius in cells, rounded up
       xa = floor_int(ux - su); xb = floor_int(ux + su);
       ya = floor_int(uy - su); yb = floor_int(uy + su);
@@ -270,26 +313,20 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
             vb = t >= c01 ? vb2 : vb;
             const int j = vb + t * kCh;
             float d[kCh];
-            if (j + kCh <= cend) {
-#pragma unroll
-              for (int c = 0; c < kCh; c++) {
-                d[c] = dist2(mpts[j + c], q2);
-                if (kCurv) d[c] = fabsf(mcurv[j + c] - qc) > ctol ? CUDART_INF_F : d[c];
-              }
+            chunk_dists<kCh, kCurv>(mpts, mcurv, j, cend, q2, qc, ctol, d);
+            if (kDense ? CCICP_CHUNK_MIN2_DENSE : CCICP_CHUNK_MIN2) {          // per chunk: its two smallest distances; the slot is resolved after the sweep
+              float lo, s2;
+              two_smallest<0, kCh, kCh>(d, lo, s2);
+              jbest = lo < best ? j : jbest;
+              second = fminf(second, fminf(fmaxf(best, lo), s2));
+              best = fminf(best, lo);
             } else {
 #pragma unroll
               for (int c = 0; c < kCh; c++) {
-                const int jc = min(j + c, cend - 1);
-                d[c] = dist2(mpts[jc], q2);
-                if (kCurv) d[c] = fabsf(mcurv[jc] - qc) > ctol ? CUDART_INF_F : d[c];
-                d[c] = j + c < cend ? d[c] : CUDART_INF_F;
+                bslot = d[c] < best ? j + c : bslot;
+                second = fminf(second, fmaxf(d[c], best));
+                best = fminf(best, d[c]);
               }
-            }
-#pragma unroll
-            for (int c = 0; c < kCh; c++) {
-              bslot = d[c] < best ? j + c : bslot;
-              second = fminf(second, fmaxf(d[c], best));
-              best = fminf(best, d[c]);
             }
           }
         } else if (kLoops && !kDense) {
@@ -325,6 +362,14 @@ NN_D void nn_search(const float2* mpts, const uint16_t* cstart, const GridP& g, 
     }
     if (r < 0) break;
     r = r == 0 ? 1 : 2 * r;
+  }
+  if ((kDense ? CCICP_CHUNK_MIN2_DENSE : CCICP_CHUNK_MIN2) && kLoops == 4 && (!kDense || CCICP_DENSE_CHUNKS) && jbest >= 0) {
+    // the chunk that lowered the bound last holds the minimum: its first slot at that distance is the answer
+    constexpr int kCh = kDense ? kRowChunkDense : kRowChunk;
+    float d[kCh];
+    chunk_dists<kCh, kCurv>(mpts, mcurv, jbest, cend, q2, qc, ctol, d);
+#pragma unroll
+    for (int c = kCh - 1; c >= 0; c--) bslot = d[c] == best ? jbest + c : bslot;
   }
   tie = (bslot >= 0 && second == best) ? 1 : 0;
 }
