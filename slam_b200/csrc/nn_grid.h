@@ -51,7 +51,7 @@ template <class T> inline T max(T a, T b) { return a > b ? a : b; }
 #define CCICP_GBIG 64      // cells per side for classes with > 512 model points
 #endif
 #ifndef CCICP_GHUGE
-#define CCICP_GHUGE 1024   // cells per side for classes with > 8192 model points (L2 variant only; C4 wave: 256 -> 30.2, 512 -> 25.4, 1024 -> 23.7 ms)
+#define CCICP_GHUGE 512    // cells per side for classes with > 8192 model points (L2 variant only; one C4 wave with the 8-slot chunk loop: 256 -> 12.7, 384 -> 12.2, 512 -> 11.9, 768 -> 12.7, 1024 -> 13.9, 1536 -> 17.0 ms; the flat loop before it preferred 1024)
 #endif
 #ifndef CCICP_CAND_UNROLL
 #define CCICP_CAND_UNROLL 2

@@ -44,7 +44,7 @@ def _device_call(ctx, pairs, prm, max_model, max_scene, hint, want_corr=True):
 @pytest.mark.parametrize("nga,nnga", [(2500, 2500), (2049, 2951), (8200, 8200), (8193, 9000)])
 def test_device_api_hint_zero_sizes_the_cell_table(ctx, nga, nnga):
     """max_cells_hint = 0: the library must assume the worst split of max_model over the two classes, including
-    both classes above 2048 and above 8192 points (grid_side steps to 128 and 1024 cells per side there)."""
+    both classes above 2048 and above 8192 points (grid_side steps to 128 and 512 cells per side there)."""
     rng = np.random.default_rng(nga)
     pairs = [_pair(rng, nga, nnga, 300, 300)]
     prm = capi.fixed_iter_params(4)
