@@ -9,6 +9,13 @@
 #include "exact_solve.cuh"
 #include "features.cuh"
 
+#ifndef CCICP_SPARSE_LOG2
+#define CCICP_SPARSE_LOG2 5
+#endif
+#ifndef CCICP_SPARSE_FIRST
+#define CCICP_SPARSE_FIRST 1      // first iteration of a seed: sparse cold pass, then every point starts from its block's sample
+#endif
+
 namespace ccicp {
 
 // block-wide sum of up to NV doubles per thread (+ two ints); result broadcast
@@ -391,7 +398,18 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
           const int par = iter & 1;
           // ---- a4..a6: transform, nearest neighbour, gate
           int pend = 0;
-          for (int i = tid; i < ns; i += kThreads) {          // loop A: search only (few live registers)
+          // (large-scan variants only: on chip the sparse pass and its barrier cost 1 % more than they save; not with the
+          // curvature gate, where a borrowed point need not be a candidate of this query at all)
+          constexpr bool kSparseFirst = CCICP_SPARSE_FIRST && kGlobal && !kCurv;
+          constexpr int kSparseMask = (1 << CCICP_SPARSE_LOG2) - 1;
+          // First iteration of a seed: nobody has a warm start.  A sparse pass (phase 0) searches every 2^CCICP_SPARSE_LOG2-th scene point
+          // cold; the full pass (phase 1) then starts a point without a match of its own from the match of the sample
+          // of its block -- a model point a few beams away bounds the search almost as well as a warm start.
+          // Later iterations run phase 1 only (a point that lost its match borrows the sample's the same way).
+          for (int phase = (kSparseFirst && iter == 0) ? 0 : 1; phase < 2; phase++) {
+          const int nq = phase ? ns : (ns + kSparseMask) >> CCICP_SPARSE_LOG2;
+          for (int q = tid; q < nq; q += kThreads) {          // loop A: search only (few live registers)
+            const int i = phase ? q : q << CCICP_SPARSE_LOG2;
             const double2 sp = s.scene[i];
             float qx, qy;
             transform(Rt, sp.x, sp.y, qx, qy);
@@ -401,6 +419,7 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               float best; int bslot, tie;
               unsigned start = s.slots[i];
               if constexpr (kTrim) { if (start == kNoSlot) start = trim_keys[i] & 0xFFFFu; }
+              if (kSparseFirst && start == kNoSlot && phase && ((i & ~kSparseMask) >= nsGA) == (i >= nsGA)) start = s.slots[i & ~kSparseMask];
               if constexpr (kCurv) {
                 const float qc = scurv[i];
                 nn_search<kGlobal, false, true, kLoops>(s.mpts, s.cstart, g, qx, qy, gate_f, start, best, bslot, tie, diag_evals, mcurv, qc, ctol);
@@ -422,6 +441,8 @@ __device__ __forceinline__ void icp_pair_body(const IcpArgs& a) {
               if constexpr (kTrim) trim_keys[i] = slot != kNoSlot ? __float_as_uint(best) : 0xFFFFFFFFu;   // the select's key
             } else if constexpr (kTrim) trim_keys[i] = 0xFFFFFFFFu;
             s.slots[i] = (uint16_t)slot;
+          }
+          if (!phase) __syncthreads();
           }
           if constexpr (kTrim) trim_select<kThreads>(a, s, ns, tid, trim_s, trim_keys);
           // ---- a7: shifted sums of the accepted pairs; every warp publishes its partials, warp 0 adds them and solves
