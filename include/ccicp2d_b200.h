@@ -214,7 +214,7 @@ int ccicp_register_batch_device_ex(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_se
  * n_pairs <= CCICP_STATIC_MAX_PAIRS, max_model and max_scene <= CCICP_STATIC_MAX_POINTS, and the pair's working set
  * must fit one SM's shared memory (the large-scan variant needs a per-CTA workspace of megabytes).  Flags that select
  * another kernel variant (EXACT_SUMS, TRIM, DIAG_COUNTS, CURV_GATE, BEST_OF_SEEDS, FIRST_BELOW) -> CCICP_E_INVALID.
- * The launch is capped to the CTAs whose replay scratch fits the array (about 230 for 1081-beam scans, 124 at 2048 points;
+ * The launch is capped to the CTAs whose replay scratch fits the array (about 220 for 1081-beam scans, 119 at 2048 points;
  * the records do not depend on the grid size).  EVERY call on a device shares the array: the counters are cleared on
  * the stream by each call, and two calls that overlap on the GPU -- different streams or ctxs without an ordering
  * between them -- race on it.                                                                                      */

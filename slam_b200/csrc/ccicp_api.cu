@@ -38,7 +38,8 @@ struct ccicp_ctx {
   bool timed = false, timed_copies = false;
   bool chunk_ramp = true;     // CCICP_CHUNK_RAMP=0: equal chunks
   int chunk_pairs = 384;      // CCICP_CHUNK_PAIRS: pairs per H2D/compute chunk of the host-buffer call
-  int stage_kb = 200;         // CCICP_STAGE_KB
+  int stage_kb = 48;          // CCICP_STAGE_KB: shared-memory staging of the large-scan tie replay; the rest of the SM's 256 KB is L1
+                              // for the workspace (one C4 wave: 8..64 KB 10.0-10.1 ms, 128 KB 10.3, 200 KB 11.0)
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the large-scan variants
   bool cluster = false;       // CCICP_CLUSTER=1: large scans run one thread-block cluster per pair (measured slower than the L2 variant on C4)
   void* timed_stream = nullptr;

@@ -194,9 +194,11 @@ struct SmemPts {
 __host__ __device__ inline size_t replay_nodes_bytes(int max_model) {
   return align_up((size_t)(2 * max_model + 16) * sizeof(kdreplay::LNode), 16);
 }
-// per CTA: the lazily built tree nodes of both classes + the rank tables of the cooperative (L2 variant) partition
+// per CTA: the lazily built tree nodes of both classes + the rank tables of the cooperative partition
+__host__ __device__ inline size_t replay_rank_bytes(int max_model) { return align_up((size_t)(max_model + 16) * sizeof(uint16_t), 16); }
+// + the global staging pair (float + u16 per model point) of splits that exceed the shared-memory staging arrays
 __host__ __device__ inline size_t replay_scratch_bytes(int max_model) {
-  return replay_nodes_bytes(max_model) + align_up((size_t)(max_model + 16) * sizeof(uint16_t), 16);
+  return replay_nodes_bytes(max_model) + replay_rank_bytes(max_model) + align_up((size_t)(max_model + 16) * 6, 16);
 }
 
 // ---- cooperative tie replay: the whole CTA walks the tied queries (listed in s.tiebits) one at a time ----------
@@ -206,6 +208,7 @@ template <int kThreads>
 struct CtaCoop {
   int tid, nt;
   float* sv; uint16_t* si; int cap; int* bcast;
+  float* gsv; uint16_t* gsi; int gcap;  // global staging for ranges beyond the shared-memory arrays (large classes)
   uint16_t* rank;                     // [>= class size] global scratch: rank tables of the data-parallel partition
   float* fred;                        // [kThreads/32][8] shared
   __device__ __forceinline__ void sync() { __syncthreads(); }
@@ -266,6 +269,10 @@ __device__ __forceinline__ void replay_ties_coop(const IcpArgs& a, const Smem& s
     co.tid = tid; co.nt = kThreads; co.cap = stage_cap;
     co.sv = (float*)stage; co.si = (uint16_t*)(stage + (size_t)stage_cap * 4);
     co.bcast = &s.misc[M_BCAST]; co.fred = fred;
+    {
+      char* gs = a.scratch + (size_t)blockIdx.x * a.scratch_per_cta + replay_nodes_bytes(a.max_model) + replay_rank_bytes(a.max_model);
+      co.gsv = (float*)gs; co.gsi = (uint16_t*)(gs + (size_t)(a.max_model + 16) * 4); co.gcap = a.max_model + 16;
+    }
     co.rank = (rank_base ? rank_base
                          : (uint16_t*)(a.scratch + (size_t)blockIdx.x * a.scratch_per_cta + replay_nodes_bytes(a.max_model))) + g.first;
     int* nn = &s.misc[M_NNODE + cls];

@@ -155,6 +155,7 @@ KD_HD bool lbox_in_range(const LNode& nd, float qx, float qy, float ballsize) {
 // `C` (the cooperation policy) provides:
 //   int tid, nt;                      this thread, threads in the group
 //   float* sv; uint16_t* si; int cap; staging arrays for `cap` elements (shared memory on the device)
+//   float* gsv; uint16_t* gsi; int gcap; a second, larger pair for ranges beyond `cap` (global memory; gcap = 0: none)
 //   int* bcast;                       one int visible to the whole group
 //   void sync();                      group barrier (also orders memory)
 //   void minmax4(float* lo, float* hi) group-wide min of lo[0..3] / max of hi[0..3], result in every thread
@@ -341,12 +342,19 @@ template <class P, class I, class C>
 KD_FN int lazy_split_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int* n_nodes, int id, C& co) {
   const LNode nd0 = nodes[id];
   const int l = nd0.l, u = nd0.u, n = u - l + 1;
+  // staging arrays: the fast ones (shared memory on the device) when the range fits, else the group's slower, larger
+  // pair (global memory: the top one or two splits of a large class); only a range beyond both is split sequentially
+  float* sv = co.sv;
+  uint16_t* si = co.si;
   if (n > co.cap) {
-    if (co.tid == 0) *co.bcast = lazy_split(pts, ind, nodes, max_nodes, n_nodes, id);
-    co.sync();
-    const int rc = *co.bcast;
-    co.sync();
-    return rc;
+    if (n <= co.gcap) { sv = co.gsv; si = co.gsi; }
+    else {
+      if (co.tid == 0) *co.bcast = lazy_split(pts, ind, nodes, max_nodes, n_nodes, id);
+      co.sync();
+      const int rc = *co.bcast;
+      co.sync();
+      return rc;
+    }
   }
   int c = -1;
   float maxspread = 0.0f;
@@ -355,24 +363,38 @@ KD_FN int lazy_split_coop(const P& pts, I* ind, LNode* nodes, int max_nodes, int
     if (sprd > maxspread) { maxspread = sprd; c = i; }
   }
   if (c < 0) return ERR_DEGENERATE;
-  float* sv = co.sv;
-  uint16_t* si = co.si;
   for (int k = co.tid; k < n; k += co.nt) {                 // gather the cut coordinate (data-parallel)
     const int o = (int)ind[l + k];
     si[k] = (uint16_t)o;
     sv[k] = coord(pts, o, c);
   }
   co.sync();
-  if (co.tid == 0) {                                        // the float mean is a sequential sum by definition (:181-186)
-    float sum = 0.0f;
-    int k = 0;
-    for (; k + 8 <= n; k += 8) {                            // loads first, then the add chain in order
-      const float a0 = sv[k], a1 = sv[k + 1], a2 = sv[k + 2], a3 = sv[k + 3];
-      const float a4 = sv[k + 4], a5 = sv[k + 5], a6 = sv[k + 6], a7 = sv[k + 7];
-      sum += a0; sum += a1; sum += a2; sum += a3; sum += a4; sum += a5; sum += a6; sum += a7;
+  // the float mean is a sequential sum by definition (:181-186): one thread adds, in order.  A range staged in the second
+  // (global-memory) pair is fed to it through the fast arrays tile by tile -- a dependent add per global load would make
+  // the top split of a 30000-point class cost as much as the rest of the replay.
+  {
+    float sum = 0.0f;                                       // meaningful on thread 0 only
+    const bool tiled = sv != co.sv;
+    for (int base = 0; base < n; base += tiled ? co.cap : n) {
+      const int m = tiled ? (n - base < co.cap ? n - base : co.cap) : n;
+      const float* tv = sv;
+      if (tiled) {
+        for (int k = co.tid; k < m; k += co.nt) co.sv[k] = sv[base + k];
+        co.sync();
+        tv = co.sv;
+      }
+      if (co.tid == 0) {
+        int k = 0;
+        for (; k + 8 <= m; k += 8) {                        // loads first, then the add chain in order
+          const float a0 = tv[k], a1 = tv[k + 1], a2 = tv[k + 2], a3 = tv[k + 3];
+          const float a4 = tv[k + 4], a5 = tv[k + 5], a6 = tv[k + 6], a7 = tv[k + 7];
+          sum += a0; sum += a1; sum += a2; sum += a3; sum += a4; sum += a5; sum += a6; sum += a7;
+        }
+        for (; k < m; k++) sum += tv[k];
+      }
+      if (tiled) co.sync();
     }
-    for (; k < n; k++) sum += sv[k];
-    *co.bcast = kd_f2i(sum / (float)n);
+    if (co.tid == 0) *co.bcast = kd_f2i(sum / (float)n);
   }
   co.sync();
   const float alpha = kd_i2f(*co.bcast);

@@ -1,3 +1,4 @@
+#include <algorithm>
 // Host build of the product's tie-replay kd-tree (slam_b200/csrc/kdreplay.h) so
 // its build + traversal can be checked on the CPU against the compiled
 // reference (oracle/_ref) without a GPU.  Test scaffolding only.
@@ -71,6 +72,7 @@ int kdr_nn_lazy(const double* pts, int n, const float* q, int nq, int32_t* idx, 
 struct HostCoop {
   int tid = 0, nt = 1;
   float* sv; uint16_t* si; int cap; int* bcast;
+  float* gsv = nullptr; uint16_t* gsi = nullptr; int gcap = 0;
   uint16_t* rank = nullptr;
   void sync() {}
   void minmax4(float*, float*) {}
@@ -111,7 +113,12 @@ int kdr_partition_both(const float* v, int n, float alpha, int nt, uint16_t* ix_
   return n - NB - 1;
 }
 
+int kdr_nn_lazy_coop_g(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis, int cap, int gcap, int* nodes_built);
 int kdr_nn_lazy_coop(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis, int cap, int* nodes_built) {
+  return kdr_nn_lazy_coop_g(pts, n, q, nq, idx, dis, cap, 0, nodes_built);
+}
+// gcap > 0: ranges beyond `cap` are staged in a second pair of arrays of gcap elements (the device's global staging)
+int kdr_nn_lazy_coop_g(const double* pts, int n, const float* q, int nq, int32_t* idx, float* dis, int cap, int gcap, int* nodes_built) {
   std::vector<kdreplay::Pt> p(n > 0 ? n : 1);
   for (int i = 0; i < n; i++) { p[i].x = (float)pts[2 * i]; p[i].y = (float)pts[2 * i + 1]; }
   std::vector<kdreplay::LNode> nodes(2 * (n > 0 ? n : 1) + 8);
@@ -119,8 +126,11 @@ int kdr_nn_lazy_coop(const double* pts, int n, const float* q, int nq, int32_t* 
   std::vector<float> sv(cap > 0 ? cap : 1);
   std::vector<uint16_t> si(cap > 0 ? cap : 1);
   int nn = 0, bc = 0;
-  std::vector<uint16_t> rank(cap > 0 ? cap : 1);
+  std::vector<uint16_t> rank(std::max(std::max(cap, gcap), 1));
+  std::vector<float> gsv(gcap > 0 ? gcap : 1);
+  std::vector<uint16_t> gsi(gcap > 0 ? gcap : 1);
   HostCoop co; co.sv = sv.data(); co.si = si.data(); co.cap = cap; co.bcast = &bc;
+  co.gsv = gsv.data(); co.gsi = gsi.data(); co.gcap = gcap;
   co.rank = cap & 1 ? nullptr : rank.data();             // an odd capacity selects the sequential partition
   kdreplay::PtrPts acc{p.data()};
   int rc = kdreplay::lazy_init_coop(acc, n, ind.data(), nodes.data(), &nn, co);

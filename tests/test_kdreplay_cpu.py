@@ -76,6 +76,20 @@ def test_cooperative_lazy_search_matches_reference(kd, oracle, cap):
         assert (idx == ridx).all() and (dis == rdis).all()
 
 
+@pytest.mark.parametrize("cap", [300, 64, 301])   # odd: sequential partition
+def test_cooperative_split_through_the_second_staging_pair(kd, oracle, cap):
+    """Ranges beyond the (shared-memory) staging capacity are staged in the larger second pair (global memory on the device)
+    instead of being split by one thread: same tree, same answers."""
+    for pts, q in clouds():
+        n, nq = len(pts), len(q)
+        ridx, rdis = oracle.nn(pts, q)
+        idx = np.full(nq, -7, np.int32); dis = np.zeros(nq, np.float32)
+        built = C.c_int(0)
+        assert kd.kdr_nn_lazy_coop_g(pts.ctypes.data_as(P), n, q.ctypes.data_as(P), nq, idx.ctypes.data_as(P),
+                                     dis.ctypes.data_as(P), cap, n + 16, C.byref(built)) == 0
+        assert (idx == ridx).all() and (dis == rdis).all()
+
+
 def test_rank_table_partition_equals_the_sequential_partition(kd):
     """part_* (kdreplay.h): the data-parallel form of select_on_coordinate_value writes the very permutation the
     reference's swap loop (kdtree.cpp:294-317) produces -- every n up to 40 with random patterns, all 2^n patterns up
