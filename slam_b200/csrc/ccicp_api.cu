@@ -210,7 +210,7 @@ int launch_icp(ccicp_ctx* ctx, int32_t pair_base, int32_t slot, int32_t n_pairs,
   const int threads = use_l2 ? kThreadsL2 : kThreadsOnChip;
   // large scans: the one-CTA-per-pair L2 variant by default; with CCICP_CLUSTER=1 one thread-block cluster per pair
   // (working sets of ~148 / kCluster pairs stay L2-resident: 0.23 GB instead of 4.6 GB of DRAM reads per wave, but the
-  // cluster barriers cost more than the DRAM latency they remove: one C4 wave 14.1 against 10.1 ms)
+  // cluster barriers cost more than the DRAM latency they remove: 7.1 k against 10.5 k pairs/s on C4)
   const bool use_cluster = use_l2 && !exact && !trim && !diag && !curv && ctx->cluster;
   int occ = 0, n_clusters = 0;
   cudaLaunchConfig_t ccfg{};
