@@ -37,7 +37,8 @@ struct ccicp_ctx {
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // h2d0,h2d1,k0,k1,d2h0,d2h1
   bool timed = false, timed_copies = false;
   bool chunk_ramp = true;     // CCICP_CHUNK_RAMP=0: equal chunks
-  int chunk_pairs = 384;      // CCICP_CHUNK_PAIRS: pairs per H2D/compute chunk of the host-buffer call
+  int chunk_pairs = 256;      // CCICP_CHUNK_PAIRS: 1081-beam pairs per H2D/compute chunk of the host-buffer call (C2 end to end: 128: 3.51,
+                              // 192: 3.48, 256: 3.49, 384: 3.53, 512: 3.56, 768: 3.66 ms)
   int stage_kb = 48;          // CCICP_STAGE_KB: shared-memory staging of the large-scan tie replay; the rest of the SM's 256 KB is L1
                               // for the workspace (one C4 wave: 8..64 KB 10.0-10.1 ms, 128 KB 10.3, 200 KB 11.0)
   bool force_l2 = false;      // diagnostics: CCICP_FORCE_L2=1 routes every batch through the large-scan variants
@@ -527,10 +528,17 @@ int ccicp_register_batch(ccicp_ctx* ctx, int32_t n_pairs, int32_t n_seeds, const
   int n_chunks = 1;
   int32_t bound[17] = {0};
   bound[1] = n_pairs;
-  if (n_seeds == 1 && !corr_idx && n_pairs >= 2 * ctx->chunk_pairs) {
+  // chunk_pairs is meant for 1081-beam pairs (34.8 KB each): larger pairs get proportionally fewer per chunk, so that the
+  // first kernel still starts after a short copy (C4's 1 MB pairs used to wait 10 ms for a first chunk of 512 pairs)
+  int cp = ctx->chunk_pairs;
+  if (n_pairs > 0) {
+    const double bytes_per_pair = ((double)n_model + (double)n_scene) * 16.0 / (double)n_pairs;
+    const double scaled = (double)ctx->chunk_pairs * 34816.0 / (bytes_per_pair > 1.0 ? bytes_per_pair : 1.0);
+    if (scaled < (double)cp) cp = scaled < 16.0 ? 16 : (int)scaled;
+  }
+  if (n_seeds == 1 && !corr_idx && n_pairs >= 2 * cp) {
     // up to 4 chunk kernels are in flight (4 streams, 4 scratch slots).  The first chunks are short so that the first
     // kernel starts after a short copy; the copies outpace the kernels, so the GPU is full a few chunks later.
-    const int cp = ctx->chunk_pairs;
     n_chunks = 0;
     int32_t pos = 0;
     if (n_pairs >= 4 * cp && ctx->chunk_ramp)
