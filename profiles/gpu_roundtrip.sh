@@ -25,7 +25,8 @@ if [ $rc -eq 0 ]; then
   ncu -i $out/icp_pair_full.ncu-rep --page source --csv --print-source sass > $out/icp_pair_full_sass.csv 2>/dev/null
   sha256sum slam_b200/lib/libccicp2d_b200.so | cut -d' ' -f1 > $out/lib_sha256.txt
   if [ "$3" == "l2" ]; then
-    timeout 900 ncu --set full --clock-control none --import-source on -k regex:icp_pair_l2_kernel\|icp_pair_cluster -s 1 -c 1 -f -o $out/large_full \
+    # (CCICP_CHUNK_PAIRS: one launch of all 148 pairs -- the host-buffer call would otherwise split 1 MB pairs into chunks of 16)
+    CCICP_CHUNK_PAIRS=100000 timeout 900 ncu --set full --clock-control none --import-source on -k regex:icp_pair_l2_kernel\|icp_pair_cluster -s 1 -c 1 -f -o $out/large_full \
         python profiles/bench_configs.py c4 --pairs 148 > $out/ncu_large.log 2>&1
     ncu -i $out/large_full.ncu-rep --page raw --csv > $out/large_full_raw.csv 2>/dev/null
   fi
