@@ -34,15 +34,19 @@ k["dram_bytes_per_launch"] = k["dram_bytes_read"] + k["dram_bytes_write"]
 # the library the capture was taken from: sha256 recorded on the GPU box next to the report (argv[4]), else the in-tree file
 sha = open(sys.argv[4]).read().strip() if len(sys.argv) > 4 else hashlib.sha256(open(os.path.join(root, 'slam_b200', 'lib', 'libccicp2d_b200.so'), 'rb').read()).hexdigest()
 tp = os.path.join(here, 'traffic.json')
-try:
-    t = json.load(open(tp))
-    if t.get("lib_sha256") != sha: t = {}
-except Exception:
-    t = {}
-t["lib_sha256"] = sha
 sys.path.insert(0, root)
 from slam_b200.build import source_sha256
-t["src_sha256"] = source_sha256()      # sources + flags in the tree now: run this right after the capture, before editing them
+src = source_sha256()                  # sources + flags in the tree now: run this right after the capture, before editing them
+try:
+    t = json.load(open(tp))
+    # captures of another library are dropped -- unless that library was built from the same sources and flags (nvcc does
+    # not reproduce binaries bit for bit): then they stay, and this capture notes the binary it came from
+    if t.get("lib_sha256") != sha and t.get("src_sha256") != src: t = {}
+except Exception:
+    t = {}
+t.setdefault("lib_sha256", sha)
+t["src_sha256"] = src
+k["lib_sha256"] = sha
 try: t["commit"] = subprocess.run(["git", "-C", root, "rev-parse", "--short", "HEAD"], stdout=subprocess.PIPE, text=True).stdout.strip()
 except Exception: pass
 t.setdefault("kernels", {})[kname] = k
