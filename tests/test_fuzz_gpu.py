@@ -76,7 +76,10 @@ def test_ragged_random_batches_on_chip(ctx, oracle, seed, exact):
     prm = capi.default_params(max_iter=15, min_delta=1e-6, indist=indist, flags=capi.F_EXACT_SUMS if exact else 0)
     run_and_compare(ctx, oracle, pairs, inits, prm, 15, 1e-6, indist, exact)
     # (CCICP_FORCE_L2=1 runs this suite through the large-scan variant: a way to fuzz it with small, ragged inputs)
-    assert ctx.launch_info().kernel_variant == (1 if os.environ.get("CCICP_FORCE_L2") == "1" else 0)
+    want = 0
+    if os.environ.get("CCICP_FORCE_L2") == "1":
+        want = 4 if os.environ.get("CCICP_CLUSTER") == "1" and not exact else 1      # (with CCICP_CLUSTER=1: the cluster variant)
+    assert ctx.launch_info().kernel_variant == want
 
 
 def test_ragged_random_batch_l2_variant(ctx, oracle):
